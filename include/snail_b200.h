@@ -1,0 +1,179 @@
+/* snail_b200 — C ABI of libsnail_b200.so.
+ *
+ * B200-native (sm_100a CUDA) replacement for the hot path of nadult/Snail: SAH-BVH traversal, ray/triangle
+ * intersection and the Whitted shading loop (shadow + one reflection bounce). The reference has no FFI layer;
+ * its seam is the C++ interface that src/render.cpp and the recursive calls in src/scene_trace.cpp use. Every
+ * entry point below names the reference interface it replaces (paths relative to the reference checkout).
+ *
+ * Conventions: handle based; every int-returning call returns 0 on success and a negative snl_status on failure
+ * (message through snl_last_error(), thread local); no exceptions cross the boundary; all pointers are caller
+ * owned; "host" pointers are ordinary host memory, "dev" pointers are CUDA device memory of the scene's device.
+ * There is no CPU fallback: without a CUDA device snl_scene_create fails with SNL_ERR_NO_DEVICE.
+ */
+#ifndef SNAIL_B200_H
+#define SNAIL_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SNL_ABI_VERSION 1
+
+typedef enum snl_status {
+	SNL_OK = 0,
+	SNL_ERR_INVALID = -1,    /* bad argument */
+	SNL_ERR_NO_DEVICE = -2,  /* no CUDA device / device index out of range */
+	SNL_ERR_CUDA = -3,       /* a CUDA runtime call failed */
+	SNL_ERR_STATE = -4,      /* call sequence error (e.g. render before set_geometry) */
+	SNL_ERR_IO = -5,         /* file could not be read / parsed */
+	SNL_ERR_UNSUPPORTED = -6 /* option the device path does not implement */
+} snl_status;
+
+typedef struct snl_scene snl_scene;
+
+/* Camera: src/camera.h:7-14 `struct Camera { float plane_dist; Vec3f pos, right, up, front; }`, passed in the
+ * order of its constructor (pos, right, up, front, plane_dist). */
+typedef struct snl_camera {
+	float pos[3], right[3], up[3], front[3];
+	float plane_dist;
+} snl_camera;
+
+/* Light: byte-compatible with src/light.h:5-17 `class Light { Vec3f pos, color; float radius, radSq, iRadius; }`. */
+typedef struct snl_light {
+	float pos[3], color[3];
+	float radius, radSq, iRadius;
+} snl_light;
+
+/* Material kinds = the shading::Material subclasses MakeMaterials can produce (src/shading/material.cpp:157-183). */
+typedef enum snl_material_kind {
+	SNL_MAT_SIMPLE = 0,     /* shading::SimpleMaterial<true>   src/shading/simple_material.h:13-30 */
+	SNL_MAT_UBER = 1,       /* shading::UberMaterial           src/shading/uber_material.h:12-31   */
+	SNL_MAT_TEX = 2,        /* shading::TexMaterial<true>      src/shading/tex_material.h:14-34    */
+	SNL_MAT_TRANSPARENT = 3 /* shading::TransparentMaterial<1> (not implemented on the device yet) */
+} snl_material_kind;
+
+/* Material::flags (src/shading/material.h:14-19) */
+enum { SNL_MATF_TEXCOORDS = 1, SNL_MATF_REFLECTION = 2, SNL_MATF_REFRACTION = 4, SNL_MATF_TRANSPARENCY = 8 };
+
+typedef struct snl_material {
+	int kind;          /* snl_material_kind */
+	int flags;         /* SNL_MATF_* */
+	float color[3];    /* Simple: colour; Uber: diffuse AFTER the x/z swap of uber_material.cpp:11 */
+	float specular[3]; /* Uber only */
+	float opacity;     /* Uber: dissolveFactor */
+	int texture;       /* Tex: index into the texture table, else -1 */
+} snl_material;
+
+/* RGB8 mip chain laid out as MipmapTexture does (src/mipmap_texture.cpp:298-308): mips stored back to back,
+ * mip m is max(w>>m,1) x max(h>>m,1), pitch 3*width, no padding. w and h must be powers of two
+ * (src/sampling/point_sampler.cpp:7-8). */
+typedef struct snl_texture {
+	const unsigned char *data; /* host */
+	size_t size;               /* total bytes of the chain */
+	int width, height, mips;
+} snl_texture;
+
+/* TreeStats analogue (src/tree_stats.h:35-113). `rays` follows TreeStats::TracingRays semantics
+ * (src/scene_trace.cpp:117,557): every traced primary ray + every shadow ray actually cast + every reflection
+ * ray + the reflection pass's shadow rays. */
+typedef struct snl_stats {
+	uint64_t rays;          /* = primary + shadow + reflection + reflection_shadow */
+	uint64_t primary;
+	uint64_t shadow;
+	uint64_t reflection;
+	uint64_t reflection_shadow;
+	uint64_t node_visits;   /* only counted when the library is built with SNL_COUNTERS */
+	uint64_t tri_tests;     /* idem */
+	float kernel_ms;        /* device time of the last call's kernels (CUDA events on the scene's stream) */
+} snl_stats;
+
+const char *snl_last_error(void);
+int snl_abi_version(void);
+int snl_device_count(void);
+
+/* Scene<BVH> life cycle (src/scene.h:13-57). One scene owns one CUDA device + one stream. */
+snl_scene *snl_scene_create(int device);
+void snl_scene_destroy(snl_scene *);
+
+/* Flatten step. Takes the host builder's output exactly as BVH holds it (src/bvh/tree.h:60-72,86-92):
+ *   nodes    BVH::Node[nNodes]     32 B  {BBox bbox; int subNode|first; short axis, firstNode | int count}
+ *   tris     Triangle[nTris]       64 B  {a, ba, ca, t0, it0, pad, plane}   src/triangle.h:133-135
+ *   shTris   ShTriangle[nTris]     64 B  {uv[3], nrm[3], matId|flat<<31}    src/triangle.h:181-230 (may be NULL)
+ *   triMatId BVH::materials[i].id  (scene material index, or ~0 = default)  src/bvh/tree.h:74-84
+ * and uploads the 64-byte two-child-box node layout + 16-byte aligned triangle records described in DESIGN.md.
+ * Float fields are copied bit for bit. */
+int snl_scene_set_geometry(snl_scene *, const void *nodes, int nNodes, const void *tris, const void *shTris,
+						   int nTris, const int *triMatId, int nMatIds);
+
+/* Scene::materials / texDict (src/scene.h:25-40, src/scene.cpp:12-21). */
+int snl_scene_set_materials(snl_scene *, const snl_material *mats, int nMats, const snl_texture *tex, int nTex);
+
+/* Scene::lights + Scene::ambientLight (src/scene.h:49-50, src/scene.cpp:9). ambient may be NULL (= 0.1,0.1,0.1). */
+int snl_scene_set_lights(snl_scene *, const snl_light *lights, int nLights, const float ambient[3]);
+
+/* The global `int gVals[16]` (src/rtbase.cpp:16). Implemented: [1] depth shading, [6] full shading,
+ * [7] reflections, [8] rank tint (uses `rank` of snl_render). [5] (stats heat-map) and [9] (4x AA) return
+ * SNL_ERR_UNSUPPORTED. */
+int snl_set_options(snl_scene *, const int gVals[16]);
+
+/* Host ingest + SAH builder (host side of the path): BaseScene::LoadWavefrontObj
+ * (src/formats/wavefront_obj.cpp:66-200), FlipNormals/GenNormals (src/base_scene.cpp:326-335,517-529),
+ * BVH::Construct (src/bvh/tree.cpp:293-328), LoadMaterialDescs/LoadTextures/MakeMaterials
+ * (src/shading/material.cpp:59-192), exactly the set-up of src/rtracer.cpp:505-586; then the flatten step.
+ * flipNormalsFlag / buildFlags as conf.flipNormals / conf.buildFlags there (flag 0 => normals ARE flipped;
+ * buildFlags: 1 noShadingData, 2 fastBuild, 4 useSah). mtlPath/texDir may be NULL. */
+int snl_scene_load_obj(snl_scene *, const char *objPath, const char *mtlPath, const char *texDir,
+					   int flipNormalsFlag, int buildFlags);
+
+/* Read back what the host builder produced (reference layouts, for parity checks against the reference's
+ * BVH::nodes/tris/shTris). Any out pointer may be NULL. */
+int snl_scene_counts(snl_scene *, int *nNodes, int *nTris, int *nMatIds, int *depth, int *nMaterials);
+int snl_scene_copy_host_bvh(snl_scene *, void *nodes, void *tris, void *shTris, int *triMatId);
+int snl_scene_bbox(snl_scene *, float bmin[3], float bmax[3]); /* BVH::GetBBox() = nodes[0].bbox */
+
+/* BVH::TraversePrimary(Context<1,0>&) on the primary rays RayGenerator::Generate produces for the full WxH image
+ * (src/ray_generator.cpp:23-47, src/render.cpp:61-62,112-115, src/bvh/traverse.cpp:14-80). Outputs (host, each
+ * may be NULL) are row-major per pixel: triId (-1 = miss), t (+inf = miss), bary2 = Context::barycentric (u,v). */
+int snl_trace_primary(snl_scene *, const snl_camera *cam, int W, int H, int *triId, float *t, float *bary2);
+
+/* BVH::TraversePrimary(Context<sharedOrigin,hasMask>&) on caller rays (AoS xyz). o3 holds one origin when
+ * sharedOrigin, else n. mask (n bytes, 0 = inactive) may be NULL. Inactive / missed rays: triId -1, t +inf. */
+int snl_trace_rays(snl_scene *, const float *o3, const float *d3, const unsigned char *mask, int n,
+				   int sharedOrigin, int *triId, float *t, float *bary2);
+
+/* BVH::TraverseShadow(ShadowContext&) (src/bvh/traverse.cpp:82-149): rays from one origin; tmax_inout[i] < 0 on
+ * input = inactive; on output occluded rays hold -inf, the others keep their value. */
+int snl_trace_shadow(snl_scene *, const float origin[3], const float *d3, float *tmax_inout, int n);
+
+/* Scene<BVH>::RayTrace(const RayGroup<sharedOrigin,hasMask>&, Cache&, Vec3q *outColor)
+ * (src/scene.h:44-46, src/scene_trace.cpp:92-520) on consecutive 256-ray packets of caller rays: ray i of a
+ * packet is lane i&3 of quad i>>2. The last packet is padded with masked-off rays. rgb3 = outColor.{x,y,z}. */
+int snl_raytrace(snl_scene *, const float *o3, const float *d3, const unsigned char *mask, int n,
+				 int sharedOrigin, float *rgb3, snl_stats *stats);
+
+/* Render() (src/render.h:16-23, src/render.cpp:214-280): the whole frame, or the tile list of the farm overload
+ * (tiles_xywh = coords, 4 ints per tile; NULL = one tile covering the image). Pixels are written at
+ * out + y*pitch + 3*x (absolute image coordinates, pitch in bytes) in ConvColor's byte order
+ * (src/render.cpp:11-17: byte0 = colour.z, byte1 = colour.y, byte2 = colour.x); pixels outside the tiles are
+ * left untouched. Tile x and w must be multiples of 16 (the packet width, src/render.cpp:52-53).
+ * snl_render: host output buffer (device->host copy included). snl_render_dev: device output buffer, asynchronous
+ * on the scene's stream until snl_scene_sync. rank only feeds the gVals[8] tint. */
+int snl_render(snl_scene *, const snl_camera *cam, int W, int H, const int *tiles_xywh, int nTiles,
+			   unsigned char *bgr8_host, size_t pitch, int rank, snl_stats *stats);
+int snl_render_dev(snl_scene *, const snl_camera *cam, int W, int H, const int *tiles_xywh, int nTiles,
+				   void *bgr8_dev, size_t pitch, int rank);
+int snl_scene_sync(snl_scene *, snl_stats *stats);
+
+/* Number of kernels this library launched on the scene since creation (bench.py's gpu_launches). */
+uint64_t snl_scene_launch_count(snl_scene *);
+
+/* cudaStream_t of the scene, as an integer, so a caller can order its own work / CUDA events after ours. */
+uint64_t snl_scene_stream(snl_scene *);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,745 @@
+// snail_b200 — extern "C" entry points of libsnail_b200.so (see include/snail_b200.h for the contract and the
+// reference interface each entry point replaces). No CPU fallback: every compute entry point launches the sm_100a
+// kernels of snl_kernels.cu on the scene's device, or fails.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+
+#include "snl_scene.h"
+
+using namespace snl;
+
+namespace snl {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(g_err, sizeof(g_err), fmt, ap);
+	va_end(ap);
+}
+
+}  // namespace snl
+
+#define SNL_CUDA(call)                                                                              \
+	do {                                                                                            \
+		cudaError_t e_ = (call);                                                                    \
+		if(e_ != cudaSuccess) {                                                                     \
+			set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+			return SNL_ERR_CUDA;                                                                    \
+		}                                                                                           \
+	} while(0)
+
+#define SNL_REQUIRE(cond, code, ...) \
+	do {                             \
+		if(!(cond)) {                \
+			set_error(__VA_ARGS__);  \
+			return code;             \
+		}                            \
+	} while(0)
+
+namespace {
+
+// ---- flatten: BVH::Node[] (own box per node) -> GpuNode[] (both child boxes per inner node) -------------------
+
+struct Flattener {
+	const std::vector<RefNode> &ref;
+	std::vector<GpuNode> out;
+	int maxDepth = 0;
+	bool bad = false;
+
+	explicit Flattener(const std::vector<RefNode> &r) : ref(r) {}
+
+	static int leaf_link(int first, int count) { return ~(first | ((count - 1) << kLeafFirstBits)); }
+
+	void set_child(int g, int c, const RefNode &box, int link) {
+		GpuNode &n = out[g];
+		Float4 &b = c == 0 ? n.b0 : n.b1;
+		b.x = box.bmin[0];
+		b.y = box.bmax[0];
+		b.z = box.bmin[1];
+		b.w = box.bmax[1];
+		if(c == 0) {
+			n.bz.x = box.bmin[2];
+			n.bz.y = box.bmax[2];
+			n.link.x = link;
+		}
+		else {
+			n.bz.z = box.bmin[2];
+			n.bz.w = box.bmax[2];
+			n.link.y = link;
+		}
+	}
+
+	// link for reference node r; leaves holding more than kLeafMaxCount triangles become a chain of inner nodes
+	// that repeat the leaf's box (same set of triangles tested, same result).
+	int link_for(int r, int depth) {
+		if(r < 0 || r >= (int)ref.size() || depth > 4096) {
+			bad = true;
+			return leaf_link(0, 1);
+		}
+		const RefNode &n = ref[r];
+		if(n.sub & 0x80000000) {
+			int first = n.sub & 0x7fffffff, count = n.count;
+			if(count < 1 || first + count > (1 << kLeafFirstBits)) {
+				bad = true;
+				return leaf_link(0, 1);
+			}
+			return chain(n, first, count, depth);
+		}
+		const int g = (int)out.size();
+		out.push_back(GpuNode());
+		memset(&out[g], 0, sizeof(GpuNode));
+		maxDepth = std::max(maxDepth, depth + 1);
+		const int sub = n.sub;
+		if(sub < 0 || sub + 1 >= (int)ref.size()) {
+			bad = true;
+			return leaf_link(0, 1);
+		}
+		const int l0 = link_for(sub, depth + 1), l1 = link_for(sub + 1, depth + 1);
+		set_child(g, 0, ref[sub], l0);
+		set_child(g, 1, ref[sub + 1], l1);
+		return g;
+	}
+
+	int chain(const RefNode &box, int first, int count, int depth) {
+		if(count <= kLeafMaxCount)
+			return leaf_link(first, count);
+		const int g = (int)out.size();
+		out.push_back(GpuNode());
+		memset(&out[g], 0, sizeof(GpuNode));
+		maxDepth = std::max(maxDepth, depth + 1);
+		const int rest = chain(box, first + kLeafMaxCount, count - kLeafMaxCount, depth + 1);
+		set_child(g, 0, box, leaf_link(first, kLeafMaxCount));
+		set_child(g, 1, box, rest);
+		return g;
+	}
+
+	bool run() {
+		out.reserve(ref.size());
+		const int root = link_for(0, 0);
+		if(root < 0) {
+			// the root itself is a leaf: node 0 = two links to it (the second visit cannot change the result:
+			// nearest-hit updates need a strictly smaller t, any-hit is idempotent)
+			out.insert(out.begin(), GpuNode());
+			memset(&out[0], 0, sizeof(GpuNode));
+			for(size_t i = 1; i < out.size(); i++) {  // chain nodes moved by one
+				if(out[i].link.x >= 0)
+					out[i].link.x++;
+				if(out[i].link.y >= 0)
+					out[i].link.y++;
+			}
+			set_child(0, 0, ref[0], root);
+			set_child(0, 1, ref[0], root);
+			maxDepth = std::max(maxDepth, 1);
+		}
+		return !bad && root <= 0;
+	}
+};
+
+int sync_and_stats(snl_scene *s, snl_stats *stats) {
+	SNL_CUDA(cudaStreamSynchronize(s->stream));
+	if(stats) {
+		Counters c;
+		SNL_CUDA(cudaMemcpy(&c, s->dCounters.ptr, sizeof(c), cudaMemcpyDeviceToHost));
+		memset(stats, 0, sizeof(*stats));
+		stats->primary = c.primary;
+		stats->shadow = c.shadow;
+		stats->reflection = c.reflection;
+		stats->reflection_shadow = c.reflection_shadow;
+		stats->rays = c.primary + c.shadow + c.reflection + c.reflection_shadow;
+		stats->node_visits = c.node_visits;
+		stats->tri_tests = c.tri_tests;
+		if(s->evPending) {
+			float ms = 0.0f;
+			if(cudaEventElapsedTime(&ms, s->ev0, s->ev1) == cudaSuccess)
+				stats->kernel_ms = ms;
+		}
+	}
+	s->evPending = false;
+	return SNL_OK;
+}
+
+int begin_call(snl_scene *s) {
+	SNL_REQUIRE(s, SNL_ERR_INVALID, "null scene");
+	SNL_CUDA(cudaSetDevice(s->device));
+	SNL_REQUIRE(s->nGpuNodes > 0, SNL_ERR_STATE, "no geometry: call snl_scene_set_geometry or snl_scene_load_obj first");
+	SNL_CUDA(cudaMemsetAsync(s->dCounters.ptr, 0, sizeof(Counters), s->stream));
+	SNL_CUDA(cudaEventRecord(s->ev0, s->stream));
+	return SNL_OK;
+}
+
+int end_call(snl_scene *s) {
+	SNL_CUDA(cudaEventRecord(s->ev1, s->stream));
+	s->evPending = true;
+	return SNL_OK;
+}
+
+// Per-origin triangle records, recomputed only when the origin changes.
+int ensure_pre(snl_scene *s, PreCacheEntry &e, const float origin[3]) {
+	if(e.valid && memcmp(e.origin, origin, 12) == 0)
+		return SNL_OK;
+	SNL_CUDA(e.buf.reserve((size_t)s->nTris));
+	SNL_CUDA(launch_pretransform(s->dTris.ptr, s->nTris, origin, e.buf.ptr, s->stream));
+	s->launches++;
+	memcpy(e.origin, origin, 12);
+	e.valid = true;
+	return SNL_OK;
+}
+
+int make_scene_dev(snl_scene *s, SceneDev &S) {
+	memset(&S, 0, sizeof(S));
+	S.nodes = s->dNodes.ptr;
+	S.gtris = s->dTris.ptr;
+	S.shtris = s->hasShading ? s->dShTris.ptr : nullptr;
+	S.triMat = s->dTriMat.ptr;
+	S.nTriMat = s->nTriMat;
+	S.mats = s->dMats.ptr;
+	S.nMats = s->nMats;
+	S.texs = s->dTexs.ptr;
+	S.nLights = (int)s->lights.size();
+	for(int i = 0; i < S.nLights; i++) {
+		const snl_light &l = s->lights[i];
+		int r = ensure_pre(s, s->lightPre[i], l.pos);
+		if(r)
+			return r;
+		S.lightPre[i] = s->lightPre[i].buf.ptr;
+		memcpy(S.lights[i].pos, l.pos, 12);
+		memcpy(S.lights[i].color, l.color, 12);
+		S.lights[i].radius = l.radius;
+		S.lights[i].radSq = l.radSq;
+		S.lights[i].iRadius = l.iRadius;
+	}
+	memcpy(S.ambient, s->ambient, 12);
+	S.gvDepth = s->gVals[1];
+	S.gvFull = s->gVals[6];
+	S.gvRefl = s->gVals[7];
+	S.gvTint = 0;
+	S.counters = s->dCounters.ptr;
+	return SNL_OK;
+}
+
+// RayGenerator::RayGenerator (src/ray_generator.cpp:4-14), same operation order.
+void make_raygen(const snl_camera &c, int W, int H, RayGenParams &g) {
+	float invW = 1.0f / float(W), invH = 1.0f / float(H);
+	invW *= float(W) / float(H);
+	const float addx[4] = {0.0f, 1.0f, 0.0f, 1.0f}, addy[4] = {0.0f, 0.0f, 1.0f, 1.0f};
+	for(int a = 0; a < 3; a++) {
+		g.origin[a] = c.pos[a];
+		g.tright[a] = c.right[a] * invW;
+		g.tup[a] = c.up[a] * invH;
+	}
+	for(int k = 0; k < 4; k++) {
+		const float taddx = addx[k] - float(W * 0.5f), taddy = addy[k] - float(H * 0.5f);
+		for(int a = 0; a < 3; a++) {
+			const float fp = c.front[a] * c.plane_dist;
+			g.txyz[a][k] = (g.tright[a] * taddx + g.tup[a] * taddy) + fp;
+		}
+	}
+}
+
+}  // namespace
+
+// =================================================================================================================
+extern "C" {
+
+const char *snl_last_error(void) { return g_err; }
+int snl_abi_version(void) { return SNL_ABI_VERSION; }
+
+int snl_device_count(void) {
+	int n = 0;
+	if(cudaGetDeviceCount(&n) != cudaSuccess) {
+		cudaGetLastError();
+		return 0;
+	}
+	return n;
+}
+
+snl_scene *snl_scene_create(int device) {
+	int n = snl_device_count();
+	if(n <= 0) {
+		set_error("no CUDA device visible: libsnail_b200 has no CPU path");
+		return nullptr;
+	}
+	if(device < 0 || device >= n) {
+		set_error("device %d out of range (have %d)", device, n);
+		return nullptr;
+	}
+	if(cudaSetDevice(device) != cudaSuccess) {
+		set_error("cudaSetDevice(%d) failed", device);
+		return nullptr;
+	}
+	snl_scene *s = new snl_scene;
+	s->device = device;
+	bool ok = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) == cudaSuccess &&
+			  cudaEventCreate(&s->ev0) == cudaSuccess && cudaEventCreate(&s->ev1) == cudaSuccess &&
+			  s->dCounters.reserve(1) == cudaSuccess;
+	if(!ok) {
+		set_error("CUDA resource creation failed: %s", cudaGetErrorString(cudaGetLastError()));
+		snl_scene_destroy(s);
+		return nullptr;
+	}
+	return s;
+}
+
+void snl_scene_destroy(snl_scene *s) {
+	if(!s)
+		return;
+	cudaSetDevice(s->device);
+	if(s->stream)
+		cudaStreamSynchronize(s->stream);
+	s->dNodes.release();
+	s->dTris.release();
+	s->dShTris.release();
+	s->dTriMat.release();
+	s->dMats.release();
+	s->dTexs.release();
+	for(auto &t : s->dTexData)
+		t.release();
+	for(auto &e : s->lightPre)
+		e.buf.release();
+	s->originPre.buf.release();
+	s->dCounters.release();
+	s->dImage.release();
+	for(auto &b : s->dScratch)
+		b.release();
+	s->dPackets.release();
+	if(s->ev0)
+		cudaEventDestroy(s->ev0);
+	if(s->ev1)
+		cudaEventDestroy(s->ev1);
+	if(s->stream)
+		cudaStreamDestroy(s->stream);
+	delete s;
+}
+
+static int upload_geometry(snl_scene *s) {
+	const HostBVH &h = s->host;
+	Flattener f(h.nodes);
+	SNL_REQUIRE(f.run(), SNL_ERR_INVALID, "malformed BVH::Node array (child / triangle range out of bounds)");
+	SNL_REQUIRE(f.maxDepth <= kStack - 2, SNL_ERR_UNSUPPORTED, "tree depth %d exceeds the traversal stack (%d)",
+				f.maxDepth, kStack - 2);
+	for(const RefNode &n : h.nodes)
+		if(n.sub & 0x80000000) {
+			long first = n.sub & 0x7fffffff;
+			SNL_REQUIRE(first + n.count <= (long)h.tris.size(), SNL_ERR_INVALID, "leaf triangle range out of bounds");
+		}
+
+	const int nTris = (int)h.tris.size();
+	std::vector<GenTri> gt(nTris);
+	for(int i = 0; i < nTris; i++) {
+		const RefTriangle &t = h.tris[i];
+		gt[i].a = {t.a[0], t.a[1], t.a[2], t.it0};
+		gt[i].ba = {t.ba[0], t.ba[1], t.ba[2], 0.0f};
+		gt[i].ca = {t.ca[0], t.ca[1], t.ca[2], 0.0f};
+		gt[i].n = {t.plane[0], t.plane[1], t.plane[2], 0.0f};
+	}
+	SNL_CUDA(cudaStreamSynchronize(s->stream));
+	SNL_CUDA(s->dNodes.reserve(f.out.size()));
+	SNL_CUDA(cudaMemcpy(s->dNodes.ptr, f.out.data(), f.out.size() * sizeof(GpuNode), cudaMemcpyHostToDevice));
+	SNL_CUDA(s->dTris.reserve(nTris));
+	SNL_CUDA(cudaMemcpy(s->dTris.ptr, gt.data(), (size_t)nTris * sizeof(GenTri), cudaMemcpyHostToDevice));
+	s->hasShading = !h.shTris.empty();
+	if(s->hasShading) {
+		SNL_CUDA(s->dShTris.reserve(nTris));
+		SNL_CUDA(cudaMemcpy(s->dShTris.ptr, h.shTris.data(), (size_t)nTris * sizeof(RefShTri), cudaMemcpyHostToDevice));
+	}
+	s->nTriMat = (int)h.triMatId.size();
+	SNL_CUDA(s->dTriMat.reserve(std::max(1, s->nTriMat)));
+	if(s->nTriMat)
+		SNL_CUDA(cudaMemcpy(s->dTriMat.ptr, h.triMatId.data(), s->nTriMat * sizeof(int), cudaMemcpyHostToDevice));
+	s->nTris = nTris;
+	s->nGpuNodes = (int)f.out.size();
+	s->gpuDepth = f.maxDepth;
+	for(auto &e : s->lightPre)
+		e.valid = false;
+	s->originPre.valid = false;
+	return SNL_OK;
+}
+
+int snl_scene_set_geometry(snl_scene *s, const void *nodes, int nNodes, const void *tris, const void *shTris, int nTris,
+						   const int *triMatId, int nMatIds) {
+	SNL_REQUIRE(s && nodes && tris, SNL_ERR_INVALID, "null argument");
+	SNL_REQUIRE(nNodes > 0 && nTris > 0, SNL_ERR_INVALID, "empty geometry (nNodes=%d nTris=%d)", nNodes, nTris);
+	SNL_REQUIRE(nTris <= (1 << kLeafFirstBits), SNL_ERR_UNSUPPORTED, "more than 2^26 triangles");
+	SNL_REQUIRE(nMatIds >= 0 && (nMatIds == 0 || triMatId), SNL_ERR_INVALID, "bad material id table");
+	SNL_CUDA(cudaSetDevice(s->device));
+	HostBVH &h = s->host;
+	h.nodes.assign((const RefNode *)nodes, (const RefNode *)nodes + nNodes);
+	h.tris.assign((const RefTriangle *)tris, (const RefTriangle *)tris + nTris);
+	if(shTris)
+		h.shTris.assign((const RefShTri *)shTris, (const RefShTri *)shTris + nTris);
+	else
+		h.shTris.clear();
+	h.triMatId.assign(triMatId, triMatId + nMatIds);
+	h.matNames.clear();
+	h.depth = 0;
+	return upload_geometry(s);
+}
+
+static int upload_materials(snl_scene *s, const snl_material *mats, int nMats, const snl_texture *tex, int nTex) {
+	SNL_CUDA(cudaSetDevice(s->device));
+	SNL_CUDA(cudaStreamSynchronize(s->stream));
+	for(int i = 0; i < nMats; i++) {
+		const snl_material &m = mats[i];
+		SNL_REQUIRE(m.kind >= SNL_MAT_SIMPLE && m.kind <= SNL_MAT_TRANSPARENT, SNL_ERR_INVALID, "material %d: bad kind", i);
+		SNL_REQUIRE(m.kind != SNL_MAT_TRANSPARENT, SNL_ERR_UNSUPPORTED,
+					"material %d: TransparentMaterial is not implemented on the device", i);
+		if(m.kind == SNL_MAT_TEX)
+			SNL_REQUIRE(m.texture >= 0 && m.texture < nTex, SNL_ERR_INVALID, "material %d: texture index", i);
+	}
+	for(auto &t : s->dTexData)
+		t.release();
+	s->dTexData.assign(nTex, DevBuf<unsigned char>());
+	std::vector<DevTexture> dt(nTex);
+	for(int i = 0; i < nTex; i++) {
+		const snl_texture &t = tex[i];
+		SNL_REQUIRE(t.data && t.width > 0 && t.height > 0 && t.mips > 0 && t.mips <= kMaxMips, SNL_ERR_INVALID,
+					"texture %d: bad description", i);
+		SNL_REQUIRE(!(t.width & (t.width - 1)) && !(t.height & (t.height - 1)), SNL_ERR_INVALID,
+					"texture %d: width & height must be a power of 2", i);
+		size_t total = 0;
+		for(int m = 0; m < t.mips; m++)
+			total += (size_t)std::max(t.width >> m, 1) * std::max(t.height >> m, 1) * 3;
+		SNL_REQUIRE(total <= t.size, SNL_ERR_INVALID, "texture %d: chain is %zu bytes, %zu given", i, total, t.size);
+		// +4: PointSampler reads 4 bytes per texel (src/sampling/point_sampler.cpp:171); we read 3, pad anyway
+		SNL_CUDA(s->dTexData[i].reserve(total + 4));
+		SNL_CUDA(cudaMemcpy(s->dTexData[i].ptr, t.data, total, cudaMemcpyHostToDevice));
+		DevTexture &d = dt[i];
+		memset(&d, 0, sizeof(d));
+		size_t off = 0;
+		for(int m = 0; m < t.mips; m++) {
+			const int w = std::max(t.width >> m, 1), hh = std::max(t.height >> m, 1);
+			d.mip[m] = s->dTexData[i].ptr + off;
+			d.pitch[m] = w * 3;
+			off += (size_t)w * hh * 3;
+		}
+		d.width = t.width;
+		d.height = t.height;
+		d.mips = t.mips;
+		d.wMul = float(t.width - 1);
+		d.hMul = float(t.height - 1);
+	}
+	SNL_CUDA(s->dTexs.reserve(std::max(1, nTex)));
+	if(nTex)
+		SNL_CUDA(cudaMemcpy(s->dTexs.ptr, dt.data(), nTex * sizeof(DevTexture), cudaMemcpyHostToDevice));
+	std::vector<DevMaterial> dm(nMats);
+	for(int i = 0; i < nMats; i++) {
+		dm[i].kind = mats[i].kind;
+		dm[i].flags = mats[i].flags;
+		memcpy(dm[i].color, mats[i].color, 12);
+		memcpy(dm[i].specular, mats[i].specular, 12);
+		dm[i].opacity = mats[i].opacity;
+		dm[i].texture = mats[i].texture;
+	}
+	SNL_CUDA(s->dMats.reserve(std::max(1, nMats)));
+	if(nMats)
+		SNL_CUDA(cudaMemcpy(s->dMats.ptr, dm.data(), nMats * sizeof(DevMaterial), cudaMemcpyHostToDevice));
+	s->nMats = nMats;
+	return SNL_OK;
+}
+
+int snl_scene_set_materials(snl_scene *s, const snl_material *mats, int nMats, const snl_texture *tex, int nTex) {
+	SNL_REQUIRE(s && nMats >= 0 && nTex >= 0 && (nMats == 0 || mats) && (nTex == 0 || tex), SNL_ERR_INVALID,
+				"bad argument");
+	return upload_materials(s, mats, nMats, tex, nTex);
+}
+
+int snl_scene_set_lights(snl_scene *s, const snl_light *lights, int nLights, const float ambient[3]) {
+	SNL_REQUIRE(s && nLights >= 0 && (nLights == 0 || lights), SNL_ERR_INVALID, "bad argument");
+	SNL_REQUIRE(nLights <= kMaxLights, SNL_ERR_UNSUPPORTED, "at most %d lights", (int)kMaxLights);
+	s->lights.assign(lights, lights + nLights);
+	if(ambient)
+		memcpy(s->ambient, ambient, 12);
+	return SNL_OK;
+}
+
+int snl_set_options(snl_scene *s, const int gVals[16]) {
+	SNL_REQUIRE(s && gVals, SNL_ERR_INVALID, "null argument");
+	SNL_REQUIRE(!gVals[5], SNL_ERR_UNSUPPORTED, "gVals[5] (packet statistics heat-map) has no per-ray equivalent");
+	SNL_REQUIRE(!gVals[9], SNL_ERR_UNSUPPORTED, "gVals[9] (4x supersampling) is not implemented yet");
+	memcpy(s->gVals, gVals, sizeof(s->gVals));
+	return SNL_OK;
+}
+
+int snl_scene_counts(snl_scene *s, int *nNodes, int *nTris, int *nMatIds, int *depth, int *nMaterials) {
+	SNL_REQUIRE(s, SNL_ERR_INVALID, "null scene");
+	if(nNodes)
+		*nNodes = (int)s->host.nodes.size();
+	if(nTris)
+		*nTris = (int)s->host.tris.size();
+	if(nMatIds)
+		*nMatIds = (int)s->host.triMatId.size();
+	if(depth)
+		*depth = s->host.depth;
+	if(nMaterials)
+		*nMaterials = s->nMats;
+	return SNL_OK;
+}
+
+int snl_scene_copy_host_bvh(snl_scene *s, void *nodes, void *tris, void *shTris, int *triMatId) {
+	SNL_REQUIRE(s, SNL_ERR_INVALID, "null scene");
+	const HostBVH &h = s->host;
+	if(nodes)
+		memcpy(nodes, h.nodes.data(), h.nodes.size() * sizeof(RefNode));
+	if(tris)
+		memcpy(tris, h.tris.data(), h.tris.size() * sizeof(RefTriangle));
+	if(shTris)
+		memcpy(shTris, h.shTris.data(), h.shTris.size() * sizeof(RefShTri));
+	if(triMatId)
+		memcpy(triMatId, h.triMatId.data(), h.triMatId.size() * sizeof(int));
+	return SNL_OK;
+}
+
+int snl_scene_bbox(snl_scene *s, float bmin[3], float bmax[3]) {
+	SNL_REQUIRE(s && !s->host.nodes.empty(), SNL_ERR_STATE, "no geometry");
+	memcpy(bmin, s->host.nodes[0].bmin, 12);
+	memcpy(bmax, s->host.nodes[0].bmax, 12);
+	return SNL_OK;
+}
+
+uint64_t snl_scene_launch_count(snl_scene *s) { return s ? s->launches : 0; }
+uint64_t snl_scene_stream(snl_scene *s) { return s ? (uint64_t)(uintptr_t)s->stream : 0; }
+
+// ---- compute entry points ---------------------------------------------------------------------------------------
+
+template <class T> static int scratch(snl_scene *s, int slot, size_t count, T **out) {
+	SNL_CUDA(s->dScratch[slot].reserve(std::max<size_t>(count * sizeof(T), 16)));
+	*out = reinterpret_cast<T *>(s->dScratch[slot].ptr);
+	return SNL_OK;
+}
+
+#define SNL_TRY(expr)    \
+	do {                 \
+		int r_ = (expr); \
+		if(r_)           \
+			return r_;   \
+	} while(0)
+
+int snl_trace_primary(snl_scene *s, const snl_camera *cam, int W, int H, int *triId, float *t, float *bary2) {
+	SNL_REQUIRE(s && cam && W > 0 && H > 0, SNL_ERR_INVALID, "bad argument");
+	SNL_TRY(begin_call(s));
+	const size_t n = (size_t)W * H;
+	int *dId = nullptr;
+	float *dT = nullptr, *dB = nullptr;
+	SNL_TRY(scratch(s, 0, n, &dId));
+	SNL_TRY(scratch(s, 1, n, &dT));
+	SNL_TRY(scratch(s, 2, n * 2, &dB));
+	SceneDev S;
+	SNL_TRY(make_scene_dev(s, S));
+	SNL_TRY(ensure_pre(s, s->originPre, cam->pos));
+	RayGenParams g;
+	make_raygen(*cam, W, H, g);
+	SNL_CUDA(launch_primary(S, s->originPre.buf.ptr, g, W, H, dId, dT, dB, s->stream));
+	s->launches++;
+	SNL_TRY(end_call(s));
+	if(triId)
+		SNL_CUDA(cudaMemcpyAsync(triId, dId, n * 4, cudaMemcpyDeviceToHost, s->stream));
+	if(t)
+		SNL_CUDA(cudaMemcpyAsync(t, dT, n * 4, cudaMemcpyDeviceToHost, s->stream));
+	if(bary2)
+		SNL_CUDA(cudaMemcpyAsync(bary2, dB, n * 8, cudaMemcpyDeviceToHost, s->stream));
+	return sync_and_stats(s, nullptr);
+}
+
+// uploads caller rays into scratch slots 0 (origins), 1 (dirs), 2 (mask)
+static int upload_rays(snl_scene *s, const float *o3, const float *d3, const unsigned char *mask, int n, int sharedOrigin,
+					   float **dO, float **dD, unsigned char **dM) {
+	const size_t no = sharedOrigin ? 1 : (size_t)n;
+	SNL_TRY(scratch(s, 0, no * 3, dO));
+	SNL_TRY(scratch(s, 1, (size_t)n * 3, dD));
+	SNL_CUDA(cudaMemcpyAsync(*dO, o3, no * 12, cudaMemcpyHostToDevice, s->stream));
+	SNL_CUDA(cudaMemcpyAsync(*dD, d3, (size_t)n * 12, cudaMemcpyHostToDevice, s->stream));
+	*dM = nullptr;
+	if(mask) {
+		SNL_TRY(scratch(s, 2, (size_t)n, dM));
+		SNL_CUDA(cudaMemcpyAsync(*dM, mask, (size_t)n, cudaMemcpyHostToDevice, s->stream));
+	}
+	return SNL_OK;
+}
+
+int snl_trace_rays(snl_scene *s, const float *o3, const float *d3, const unsigned char *mask, int n, int sharedOrigin,
+				   int *triId, float *t, float *bary2) {
+	SNL_REQUIRE(s && o3 && d3 && n >= 0, SNL_ERR_INVALID, "bad argument");
+	if(n == 0)
+		return SNL_OK;
+	SNL_TRY(begin_call(s));
+	float *dO, *dD;
+	unsigned char *dM;
+	SNL_TRY(upload_rays(s, o3, d3, mask, n, sharedOrigin, &dO, &dD, &dM));
+	// results: one scratch slot holding triId | t | bary
+	unsigned char *res = nullptr;
+	SNL_TRY(scratch(s, 3, (size_t)n * 16, &res));
+	int *dId = (int *)res;
+	float *dT = (float *)(res + (size_t)n * 4), *dB = (float *)(res + (size_t)n * 8);
+	SceneDev S;
+	SNL_TRY(make_scene_dev(s, S));
+	if(sharedOrigin)
+		SNL_TRY(ensure_pre(s, s->originPre, o3));
+	SNL_CUDA(launch_trace_rays(S, s->originPre.buf.ptr, dO, dD, dM, n, sharedOrigin != 0, dId, dT, dB, s->stream));
+	s->launches++;
+	SNL_TRY(end_call(s));
+	if(triId)
+		SNL_CUDA(cudaMemcpyAsync(triId, dId, (size_t)n * 4, cudaMemcpyDeviceToHost, s->stream));
+	if(t)
+		SNL_CUDA(cudaMemcpyAsync(t, dT, (size_t)n * 4, cudaMemcpyDeviceToHost, s->stream));
+	if(bary2)
+		SNL_CUDA(cudaMemcpyAsync(bary2, dB, (size_t)n * 8, cudaMemcpyDeviceToHost, s->stream));
+	return sync_and_stats(s, nullptr);
+}
+
+int snl_trace_shadow(snl_scene *s, const float origin[3], const float *d3, float *tmax_inout, int n) {
+	SNL_REQUIRE(s && origin && d3 && tmax_inout && n >= 0, SNL_ERR_INVALID, "bad argument");
+	if(n == 0)
+		return SNL_OK;
+	SNL_TRY(begin_call(s));
+	float *dD, *dT;
+	SNL_TRY(scratch(s, 1, (size_t)n * 3, &dD));
+	SNL_TRY(scratch(s, 3, (size_t)n, &dT));
+	SNL_CUDA(cudaMemcpyAsync(dD, d3, (size_t)n * 12, cudaMemcpyHostToDevice, s->stream));
+	SNL_CUDA(cudaMemcpyAsync(dT, tmax_inout, (size_t)n * 4, cudaMemcpyHostToDevice, s->stream));
+	SceneDev S;
+	SNL_TRY(make_scene_dev(s, S));
+	SNL_TRY(ensure_pre(s, s->originPre, origin));
+	SNL_CUDA(launch_trace_shadow(S, s->originPre.buf.ptr, origin, dD, dT, n, s->stream));
+	s->launches++;
+	SNL_TRY(end_call(s));
+	SNL_CUDA(cudaMemcpyAsync(tmax_inout, dT, (size_t)n * 4, cudaMemcpyDeviceToHost, s->stream));
+	return sync_and_stats(s, nullptr);
+}
+
+int snl_raytrace(snl_scene *s, const float *o3, const float *d3, const unsigned char *mask, int n, int sharedOrigin,
+				 float *rgb3, snl_stats *stats) {
+	SNL_REQUIRE(s && o3 && d3 && rgb3 && n >= 0, SNL_ERR_INVALID, "bad argument");
+	if(n == 0)
+		return SNL_OK;
+	SNL_TRY(begin_call(s));
+	float *dO, *dD, *dC;
+	unsigned char *dM;
+	SNL_TRY(upload_rays(s, o3, d3, mask, n, sharedOrigin, &dO, &dD, &dM));
+	SNL_TRY(scratch(s, 3, (size_t)n * 3, &dC));
+	SceneDev S;
+	SNL_TRY(make_scene_dev(s, S));
+	if(sharedOrigin)
+		SNL_TRY(ensure_pre(s, s->originPre, o3));
+	SNL_CUDA(launch_raytrace(S, s->originPre.buf.ptr, dO, dD, dM, n, sharedOrigin != 0, dC, s->stream));
+	s->launches++;
+	SNL_TRY(end_call(s));
+	SNL_CUDA(cudaMemcpyAsync(rgb3, dC, (size_t)n * 12, cudaMemcpyDeviceToHost, s->stream));
+	return sync_and_stats(s, stats);
+}
+
+// Tile list -> packet list (RenderTask::Work's x/y loops, src/render.cpp:67-68), cached between calls.
+static int ensure_packets(snl_scene *s, const int *tiles, int nTiles, int W, int H) {
+	std::vector<int> key(tiles, tiles + (size_t)nTiles * 4);
+	key.push_back(W);
+	key.push_back(H);
+	if(key == s->lastTiles && s->dPackets.ptr)
+		return SNL_OK;
+	std::vector<int4> packets;
+	for(int i = 0; i < nTiles; i++) {
+		const int x = tiles[i * 4 + 0], y = tiles[i * 4 + 1], w = tiles[i * 4 + 2], h = tiles[i * 4 + 3];
+		SNL_REQUIRE(x >= 0 && y >= 0 && w > 0 && h > 0 && x + w <= W && y + h <= H, SNL_ERR_INVALID,
+					"tile %d (%d,%d,%d,%d) outside the %dx%d image", i, x, y, w, h, W, H);
+		SNL_REQUIRE(x % 16 == 0 && (w % 16 == 0 || x + w == W), SNL_ERR_INVALID,
+					"tile %d: x and w must be multiples of the packet width 16", i);
+		for(int py = 0; py < h; py += 16)
+			for(int px = 0; px < w; px += 16)
+				packets.push_back(make_int4(x + px, y + py, std::min(16, w - px), std::min(16, h - py)));
+	}
+	SNL_CUDA(cudaStreamSynchronize(s->stream));
+	SNL_CUDA(s->dPackets.reserve(std::max<size_t>(packets.size(), 1)));
+	if(!packets.empty())
+		SNL_CUDA(cudaMemcpy(s->dPackets.ptr, packets.data(), packets.size() * sizeof(int4), cudaMemcpyHostToDevice));
+	s->nPackets = (int)packets.size();
+	s->lastTiles.swap(key);
+	return SNL_OK;
+}
+
+static const float kRankTint[16][3] = {  // src/render.cpp:119-128
+	{0.6f, 0.6f, 0.6f}, {0.6f, 0.6f, 1.0f}, {0.6f, 1.0f, 0.6f}, {0.6f, 1.0f, 1.0f}, {1.0f, 0.6f, 0.6f}, {1.0f, 0.6f, 1.0f},
+	{1.0f, 1.0f, 0.6f}, {1.0f, 1.0f, 1.0f}, {0.3f, 0.3f, 0.3f}, {0.3f, 0.3f, 1.0f}, {0.3f, 0.7f, 0.3f}, {0.3f, 0.7f, 0.7f},
+	{0.7f, 0.3f, 0.3f}, {0.7f, 0.3f, 0.7f}, {0.7f, 0.7f, 0.3f}, {0.7f, 1.7f, 0.7f}};
+
+static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, const int *tiles, int nTiles, unsigned char *dOut,
+						 size_t pitch, int rank) {
+	SceneDev S;
+	SNL_TRY(make_scene_dev(s, S));
+	if(s->gVals[8]) {
+		S.gvTint = 1;
+		memcpy(S.tint, kRankTint[(unsigned)rank % 16], 12);
+	}
+	SNL_TRY(ensure_pre(s, s->originPre, cam->pos));
+	RayGenParams g;
+	make_raygen(*cam, W, H, g);
+	const int4 *packets = nullptr;
+	if(tiles) {
+		SNL_TRY(ensure_packets(s, tiles, nTiles, W, H));
+		packets = s->dPackets.ptr;
+	}
+	SNL_CUDA(launch_render(S, s->originPre.buf.ptr, g, W, H, packets, s->nPackets, dOut, pitch, s->stream));
+	s->launches++;
+	return SNL_OK;
+}
+
+int snl_render_dev(snl_scene *s, const snl_camera *cam, int W, int H, const int *tiles_xywh, int nTiles, void *bgr8_dev,
+				   size_t pitch, int rank) {
+	SNL_REQUIRE(s && cam && bgr8_dev && W > 0 && H > 0 && pitch >= (size_t)W * 3, SNL_ERR_INVALID, "bad argument");
+	SNL_REQUIRE(!tiles_xywh || nTiles >= 0, SNL_ERR_INVALID, "bad tile list");
+	SNL_TRY(begin_call(s));
+	SNL_TRY(render_common(s, cam, W, H, tiles_xywh, nTiles, (unsigned char *)bgr8_dev, pitch, rank));
+	return end_call(s);
+}
+
+int snl_scene_sync(snl_scene *s, snl_stats *stats) {
+	SNL_REQUIRE(s, SNL_ERR_INVALID, "null scene");
+	SNL_CUDA(cudaSetDevice(s->device));
+	return sync_and_stats(s, stats);
+}
+
+int snl_render(snl_scene *s, const snl_camera *cam, int W, int H, const int *tiles_xywh, int nTiles,
+			   unsigned char *bgr8_host, size_t pitch, int rank, snl_stats *stats) {
+	SNL_REQUIRE(s && cam && bgr8_host && W > 0 && H > 0 && pitch >= (size_t)W * 3, SNL_ERR_INVALID, "bad argument");
+	SNL_REQUIRE(!tiles_xywh || nTiles >= 0, SNL_ERR_INVALID, "bad tile list");
+	SNL_TRY(begin_call(s));
+	const size_t dpitch = (size_t)W * 3;
+	SNL_CUDA(s->dImage.reserve(dpitch * H));
+	SNL_TRY(render_common(s, cam, W, H, tiles_xywh, nTiles, s->dImage.ptr, dpitch, rank));
+	SNL_TRY(end_call(s));
+	if(!tiles_xywh)
+		SNL_CUDA(cudaMemcpy2DAsync(bgr8_host, pitch, s->dImage.ptr, dpitch, dpitch, H, cudaMemcpyDeviceToHost, s->stream));
+	else
+		for(int i = 0; i < nTiles; i++) {
+			const int x = tiles_xywh[i * 4 + 0], y = tiles_xywh[i * 4 + 1], w = tiles_xywh[i * 4 + 2], h = tiles_xywh[i * 4 + 3];
+			SNL_CUDA(cudaMemcpy2DAsync(bgr8_host + (size_t)y * pitch + (size_t)x * 3, pitch,
+									   s->dImage.ptr + (size_t)y * dpitch + (size_t)x * 3, dpitch, (size_t)w * 3, h,
+									   cudaMemcpyDeviceToHost, s->stream));
+		}
+	return sync_and_stats(s, stats);
+}
+
+int snl_scene_load_obj(snl_scene *s, const char *objPath, const char *mtlPath, const char *texDir, int flipNormalsFlag,
+					   int buildFlags) {
+	SNL_REQUIRE(s && objPath, SNL_ERR_INVALID, "null argument");
+	SNL_CUDA(cudaSetDevice(s->device));
+	HostScene hs;
+	std::string err;
+	if(!load_obj_scene(objPath, mtlPath, texDir, flipNormalsFlag, buildFlags, hs, err)) {
+		set_error("%s", err.c_str());
+		return SNL_ERR_IO;
+	}
+	s->host = std::move(hs.bvh);
+	SNL_TRY(upload_geometry(s));
+	std::vector<snl_material> mats;
+	for(auto &m : hs.mats)
+		mats.push_back(m.m);
+	std::vector<snl_texture> texs;
+	for(auto &t : hs.texs)
+		texs.push_back(snl_texture{t.data.data(), t.data.size(), t.width, t.height, t.mips});
+	return upload_materials(s, mats.data(), (int)mats.size(), texs.data(), (int)texs.size());
+}
+
+}  // extern "C"

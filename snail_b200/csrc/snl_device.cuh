@@ -1,0 +1,607 @@
+// snail_b200 — device code of the hot path (sm_100a). Compiled with -fmad=false: every expression below is
+// written in the reference's operation order so that, with IEEE division / square root, results are bit-identical
+// to the reference built on veclib's scalar back-end (veclib/scalar/f32.h:102-111: Inv = 1/x, RSqrt = 1/sqrt(x)).
+//
+// One thread = one ray. One CTA of 256 threads = one reference packet (64 quads, src/render.cpp:52-66): thread i is
+// lane i&3 of quad i>>2; a half-warp is one 4-quad shading block (src/scene_trace.cpp:98,146).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <math_constants.h>
+
+#include "snl_types.h"
+
+namespace snl {
+
+#define SNL_FULL 0xffffffffu
+
+enum { kStack = 96, kPacket = 256 };
+
+struct SceneDev {
+	const GpuNode *nodes;
+	const GenTri *gtris;
+	const RefShTri *shtris;  // null: no shading data (BVH::noShadingData)
+	const int *triMat;       // BVH::materials[i].id
+	const DevMaterial *mats;
+	const DevTexture *texs;
+	const PreTri *lightPre[kMaxLights];
+	DevLight lights[kMaxLights];
+	int nTriMat, nMats, nLights;
+	float ambient[3];
+	int gvDepth, gvFull, gvRefl, gvTint;  // gVals[1], [6], [7], [8]
+	float tint[3];
+	Counters *counters;
+};
+
+__device__ __forceinline__ float4 ldg4(const Float4 *p) { return __ldg(reinterpret_cast<const float4 *>(p)); }
+__device__ __forceinline__ int4 ldg4(const Int4 *p) { return __ldg(reinterpret_cast<const int4 *>(p)); }
+
+#ifdef SNL_COUNTERS
+#define SNL_COUNT(var) (++(var))
+#else
+#define SNL_COUNT(var) ((void)0)
+#endif
+
+struct TravCount {
+	unsigned nodes, tris;
+};
+
+// BBox::Test, one ray vs one box (src/bounding_box.cpp:61-97): hit <=> lmax >= 0 && lmin <= min(lmax, dist).
+__device__ __forceinline__ bool box_test(float minx, float maxx, float miny, float maxy, float minz, float maxz, float ox,
+										 float oy, float oz, float ix, float iy, float iz, float dist, float &lminOut) {
+	float l1 = ix * (minx - ox), l2 = ix * (maxx - ox);
+	float lmin = fminf(l1, l2), lmax = fmaxf(l1, l2);
+	l1 = iy * (miny - oy);
+	l2 = iy * (maxy - oy);
+	lmin = fmaxf(lmin, fminf(l1, l2));
+	lmax = fminf(lmax, fmaxf(l1, l2));
+	l1 = iz * (minz - oz);
+	l2 = iz * (maxz - oz);
+	lmin = fmaxf(lmin, fminf(l1, l2));
+	lmax = fminf(lmax, fmaxf(l1, l2));
+	lminOut = lmin;
+	return lmax >= 0.0f && lmin <= fminf(lmax, dist);
+}
+
+struct Hit {
+	float dist;
+	int obj;
+	float bu, bv;
+};
+
+// Triangle::Collide(Context<1,*>&) per ray (src/triangle.cpp:3-63), sharedOrigin form with the per-origin
+// precomputation already applied (PreTri).
+__device__ __forceinline__ void tri_nearest_pre(const PreTri *__restrict__ t, int idx, float dx, float dy, float dz, Hit &h) {
+	const float4 tu = ldg4(&t->u), tv = ldg4(&t->v), tn = ldg4(&t->n);
+	const float det = dx * tn.x + dy * tn.y + dz * tn.z;
+	const float v = dx * tv.x + dy * tv.y + dz * tv.z;
+	const float u = dx * tu.x + dy * tu.y + dz * tu.z;
+	const float duv = det - u - v;
+	const float uvmin = fminf(u, fminf(v, duv));
+	const float uvmax = fmaxf(u, fmaxf(v, duv));
+	if(uvmax <= 0.0f || uvmin >= 0.0f) {
+		const float idet = 1.0f / det;
+		const float dist = idet * tu.w;
+		if(dist < h.dist && dist > 0.0f) {
+			h.dist = dist;
+			h.obj = idx;
+			h.bu = u * idet;
+			h.bv = v * idet;
+		}
+	}
+}
+
+// Triangle::Collide(Context<0,*>&) per ray (src/triangle.cpp:29-37,41-61): per-ray origin.
+__device__ __forceinline__ void tri_nearest_gen(const GenTri *__restrict__ t, int idx, float ox, float oy, float oz,
+												float dx, float dy, float dz, Hit &h) {
+	const float4 ta = ldg4(&t->a), tba = ldg4(&t->ba), tca = ldg4(&t->ca), tn = ldg4(&t->n);
+	const float det = dx * tn.x + dy * tn.y + dz * tn.z;
+	const float tx = ox - ta.x, ty = oy - ta.y, tz = oz - ta.z;
+	// tvec0 = ba ^ tvec, tvec1 = tvec ^ ca   (veclib/vec3.h:101-106)
+	const float t0x = tba.y * tz - tba.z * ty, t0y = tba.z * tx - tba.x * tz, t0z = tba.x * ty - tba.y * tx;
+	const float t1x = ty * tca.z - tz * tca.y, t1y = tz * tca.x - tx * tca.z, t1z = tx * tca.y - ty * tca.x;
+	const float tmul = -(tx * tn.x + ty * tn.y + tz * tn.z);
+	const float v = (dx * t0x + dy * t0y + dz * t0z) * ta.w;
+	const float u = (dx * t1x + dy * t1y + dz * t1z) * ta.w;
+	const float duv = det - u - v;
+	const float uvmin = fminf(u, fminf(v, duv));
+	const float uvmax = fmaxf(u, fmaxf(v, duv));
+	if(uvmax <= 0.0f || uvmin >= 0.0f) {
+		const float idet = 1.0f / det;
+		const float dist = idet * tmul;
+		if(dist < h.dist && dist > 0.0f) {
+			h.dist = dist;
+			h.obj = idx;
+			h.bu = u * idet;
+			h.bv = v * idet;
+		}
+	}
+}
+
+// BVH::TraversePrimaryN per ray (src/bvh/traverse.cpp:14-80). Per-thread stack, children visited nearest first
+// (by slab entry distance instead of the packet's firstNode^sign[axis]; only exact-t ties can differ).
+template <bool SHARED>
+__device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nodes, const void *__restrict__ tris,
+												 float ox, float oy, float oz, float dx, float dy, float dz, float ix,
+												 float iy, float iz, Hit &h, TravCount &tc) {
+	int stack[kStack];
+	int sp = 0;
+	int cur = 0;
+	for(;;) {
+		if(cur >= 0) {
+			SNL_COUNT(tc.nodes);
+			const GpuNode *n = nodes + cur;
+			const float4 b0 = ldg4(&n->b0), b1 = ldg4(&n->b1), bz = ldg4(&n->bz);
+			const int4 link = ldg4(&n->link);
+			float lmin0, lmin1;
+			const bool h0 = box_test(b0.x, b0.y, b0.z, b0.w, bz.x, bz.y, ox, oy, oz, ix, iy, iz, h.dist, lmin0);
+			const bool h1 = box_test(b1.x, b1.y, b1.z, b1.w, bz.z, bz.w, ox, oy, oz, ix, iy, iz, h.dist, lmin1);
+			if(h0 && h1) {
+				const bool swap = lmin1 < lmin0;
+				stack[sp++] = swap ? link.x : link.y;
+				cur = swap ? link.y : link.x;
+				continue;
+			}
+			if(h0) {
+				cur = link.x;
+				continue;
+			}
+			if(h1) {
+				cur = link.y;
+				continue;
+			}
+		}
+		else {
+			const int leaf = ~cur;
+			const int first = leaf & kLeafFirstMask, count = (leaf >> kLeafFirstBits) + 1;
+			for(int i = 0; i < count; i++) {
+				SNL_COUNT(tc.tris);
+				if(SHARED)
+					tri_nearest_pre(reinterpret_cast<const PreTri *>(tris) + first + i, first + i, dx, dy, dz, h);
+				else
+					tri_nearest_gen(reinterpret_cast<const GenTri *>(tris) + first + i, first + i, ox, oy, oz, dx, dy,
+									dz, h);
+			}
+		}
+		if(sp == 0)
+			break;
+		cur = stack[--sp];
+	}
+}
+
+// BVH::TraverseShadow per ray (src/bvh/traverse.cpp:82-149) with Triangle::Collide(ShadowContext&)
+// (src/triangle.cpp:65-102): any hit, ONE-SIDED (only triangles with dir.nrm >= u+v >= 0 occlude), no division.
+// Origin = light position, so triangles are PreTri records of that light.
+__device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ nodes, const PreTri *__restrict__ tris, float ox,
+												float oy, float oz, float dx, float dy, float dz, float ix, float iy,
+												float iz, float dist, TravCount &tc) {
+	int stack[kStack];
+	int sp = 0;
+	int cur = 0;
+	for(;;) {
+		if(cur >= 0) {
+			SNL_COUNT(tc.nodes);
+			const GpuNode *n = nodes + cur;
+			const float4 b0 = ldg4(&n->b0), b1 = ldg4(&n->b1), bz = ldg4(&n->bz);
+			const int4 link = ldg4(&n->link);
+			float lmin0, lmin1;
+			const bool h0 = box_test(b0.x, b0.y, b0.z, b0.w, bz.x, bz.y, ox, oy, oz, ix, iy, iz, dist, lmin0);
+			const bool h1 = box_test(b1.x, b1.y, b1.z, b1.w, bz.z, bz.w, ox, oy, oz, ix, iy, iz, dist, lmin1);
+			if(h0 && h1) {
+				const bool swap = lmin1 < lmin0;
+				stack[sp++] = swap ? link.x : link.y;
+				cur = swap ? link.y : link.x;
+				continue;
+			}
+			if(h0) {
+				cur = link.x;
+				continue;
+			}
+			if(h1) {
+				cur = link.y;
+				continue;
+			}
+		}
+		else {
+			const int leaf = ~cur;
+			const int first = leaf & kLeafFirstMask, count = (leaf >> kLeafFirstBits) + 1;
+			for(int i = 0; i < count; i++) {
+				SNL_COUNT(tc.tris);
+				const PreTri *t = tris + first + i;
+				const float4 tu = ldg4(&t->u), tv = ldg4(&t->v), tn = ldg4(&t->n);
+				const float det = dx * tn.x + dy * tn.y + dz * tn.z;
+				const float v = dx * tv.x + dy * tv.y + dz * tv.z;
+				const float u = dx * tu.x + dy * tu.y + dz * tu.z;
+				const float tmul = tu.w;
+				if(fminf(u, v) >= 0.0f && u + v <= det && tmul > 0.0f && tmul < dist * det)
+					return true;
+			}
+		}
+		if(sp == 0)
+			break;
+		cur = stack[--sp];
+	}
+	return false;
+}
+
+// Triangle::Collide sharedOrigin precomputation (src/triangle.cpp:9-18) for every triangle and one origin.
+__global__ void __launch_bounds__(256) k_pretransform(const GenTri *__restrict__ gtris, int nTris, float ox, float oy,
+													 float oz, PreTri *__restrict__ out) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= nTris)
+		return;
+	const float4 ta = ldg4(&gtris[i].a), tba = ldg4(&gtris[i].ba), tca = ldg4(&gtris[i].ca), tn = ldg4(&gtris[i].n);
+	const float it0 = ta.w;
+	const float tx = ox - ta.x, ty = oy - ta.y, tz = oz - ta.z;
+	float4 u, v, n;
+	// tvec0 = (ba ^ tvec) * it0
+	v.x = (tba.y * tz - tba.z * ty) * it0;
+	v.y = (tba.z * tx - tba.x * tz) * it0;
+	v.z = (tba.x * ty - tba.y * tx) * it0;
+	v.w = 0.0f;
+	// tvec1 = (tvec ^ ca) * it0
+	u.x = (ty * tca.z - tz * tca.y) * it0;
+	u.y = (tz * tca.x - tx * tca.z) * it0;
+	u.z = (tx * tca.y - ty * tca.x) * it0;
+	u.w = -(tx * tn.x + ty * tn.y + tz * tn.z);
+	n = make_float4(tn.x, tn.y, tn.z, 0.0f);
+	float4 *o = reinterpret_cast<float4 *>(out + i);
+	o[0] = u;
+	o[1] = v;
+	o[2] = n;
+}
+
+// SafeInv (src/rtbase.h:117-119): Inv(v + 1e-8).
+__device__ __forceinline__ float safe_inv(float v) { return 1.0f / (v + 0.00000001f); }
+
+// RayGenerator::Generate (src/ray_generator.cpp:23-47) for thread (tx, ty) of the 16x16 packet at (x0, y0).
+__device__ __forceinline__ void gen_primary(const RayGenParams &g, int x0, int y0, int tx, int ty, float &dx, float &dy,
+											float &dz) {
+	const int k = tx & 3, j = tx >> 2;
+	const float xoff = float(x0 + (k & 2));        // floatq xoff(x + 0, x + 0, x + 2, x + 2)
+	const float yoff = float(y0 - (k >> 1));       // floatq yoff(y + 0, y + 0, y - 1, y - 1)
+	const float tposx = float(4 * j) + xoff;
+	const float tposy = float(ty) + yoff;
+	const float tpx = g.tup[0] * tposy + g.txyz[0][k];
+	const float tpy = g.tup[1] * tposy + g.txyz[1][k];
+	const float tpz = g.tup[2] * tposy + g.txyz[2][k];
+	const float px = g.tright[0] * tposx + tpx;
+	const float py = g.tright[1] * tposx + tpy;
+	const float pz = g.tright[2] * tposx + tpz;
+	const float r = 1.0f / sqrtf(px * px + py * py + pz * pz);
+	dx = px * r;
+	dy = py * r;
+	dz = pz * r;
+}
+
+struct Sample {
+	float px, py, pz;  // position
+	float nx, ny, nz;  // normal (not normalised when interpolated, src/scene_trace.cpp:204,220,249)
+	float dr, dg, db;  // diffuse
+	float sr, sg, sb;  // specular
+};
+
+__device__ __forceinline__ float quad_min(float v) {
+	v = fminf(v, __shfl_xor_sync(SNL_FULL, v, 1));
+	return fminf(v, __shfl_xor_sync(SNL_FULL, v, 2));
+}
+__device__ __forceinline__ float quad_max(float v) {
+	v = fmaxf(v, __shfl_xor_sync(SNL_FULL, v, 1));
+	return fmaxf(v, __shfl_xor_sync(SNL_FULL, v, 2));
+}
+
+// PointSampler::Sample (src/sampling/point_sampler.cpp:126-210): bilinear RGB8 fetch, vertical flip,
+// mip picked from the quad's texDiff.
+__device__ __forceinline__ void tex_sample(const DevTexture &T, float tu, float tv, float tdx, float tdy, float &r, float &g,
+										   float &b) {
+	// ClampTexCoord (point_sampler.cpp:43-51)
+	float ux = tu - float(int(tu)), uy = tv - float(int(tv));
+	ux = ux < 0.0f ? ux + 1.0f : ux;
+	uy = uy < 0.0f ? uy + 1.0f : uy;
+	const float posx = ux * T.wMul, posy = uy * T.hMul;
+
+	unsigned mip = 0;
+	{
+		const float mn = fminf(tdx * T.wMul, tdy * T.hMul);
+		unsigned pixels = unsigned(mn * 0.6f);
+		while(pixels) {
+			mip++;
+			pixels >>= 1;
+		}
+		mip = min(mip, unsigned(T.mips - 1));
+	}
+	const unsigned char *data = T.mip[mip];
+	const int pitch = T.pitch[mip];
+
+	int x1 = int(posx), y1 = int(posy);
+	int x2 = x1 + 1, y2 = y1 + 1;
+	const float fx = posx - float(x1), fy = posy - float(y1);
+	y1 = T.height - y1;
+	y2 = T.height - y2;
+	const int wm = (T.width - 1) >> mip, hm = (T.height - 1) >> mip;
+	x1 = ((x1 >> mip) & wm) * 3;
+	x2 = ((x2 >> mip) & wm) * 3;
+	y1 = ((y1 >> mip) & hm) * pitch;
+	y2 = ((y2 >> mip) & hm) * pitch;
+	const unsigned char *p0 = data + x1 + y1, *p1 = data + x2 + y1, *p2 = data + x1 + y2, *p3 = data + x2 + y2;
+	const float r0 = float(__ldg(p0 + 0)), g0 = float(__ldg(p0 + 1)), b0 = float(__ldg(p0 + 2));
+	const float r1 = float(__ldg(p1 + 0)), g1 = float(__ldg(p1 + 1)), b1 = float(__ldg(p1 + 2));
+	const float r2 = float(__ldg(p2 + 0)), g2 = float(__ldg(p2 + 1)), b2 = float(__ldg(p2 + 2));
+	const float r3 = float(__ldg(p3 + 0)), g3 = float(__ldg(p3 + 1)), b3 = float(__ldg(p3 + 2));
+	// Lerp(a, b, x) = a + (b - a) * x   (veclib/vecbase.h:80)
+	const float ra = r0 + (r1 - r0) * fx, rb = r2 + (r3 - r2) * fx;
+	const float ga = g0 + (g1 - g0) * fx, gb = g2 + (g3 - g2) * fx;
+	const float ba = b0 + (b1 - b0) * fx, bb = b2 + (b3 - b2) * fx;
+	const float k = 1.0f / 255.0f;
+	r = (ra + (rb - ra) * fy) * k;
+	g = (ga + (gb - ga) * fy) * k;
+	b = (ba + (bb - ba) * fy) * k;
+}
+
+// mat->Shade (src/shading/*.h Shade_) for one lane. matId == -1 (~0): Scene::defaultMat = white SimpleMaterial<true>.
+__device__ __forceinline__ void material_shade(const SceneDev &S, int matId, bool masked, float dx, float dy, float dz,
+											   float tu, float tv, float tdx, float tdy, Sample &s) {
+	const float dot = dx * s.nx + dy * s.ny + dz * s.nz;
+	if(matId < 0) {
+		const float a = fabsf(dot);
+		s.dr = s.dg = s.db = a;  // Vec3q(1,1,1) * Abs(dir | normal)
+		s.sr = s.sg = s.sb = a;
+		return;
+	}
+	const DevMaterial &m = S.mats[matId];
+	if(m.kind == 2 /* SNL_MAT_TEX */) {
+		float r, g, b;
+		tex_sample(S.texs[m.texture], tu, tv, tdx, tdy, r, g, b);
+		s.dr = r * dot;
+		s.dg = g * dot;
+		s.db = b * dot;
+		s.sr = s.dr;
+		s.sg = s.dg;
+		s.sb = s.db;
+	}
+	else {
+		const float a = fabsf(dot);
+		s.dr = m.color[0] * a;
+		s.dg = m.color[1] * a;
+		s.db = m.color[2] * a;
+		if(m.kind == 1 /* SNL_MAT_UBER */ && masked) {
+			// UberMaterial::Shade_ hasMask branch stores the material's specular colour, the other branch the
+			// diffuse term (src/shading/uber_material.h:21-29)
+			s.sr = m.specular[0];
+			s.sg = m.specular[1];
+			s.sb = m.specular[2];
+		}
+		else {
+			s.sr = s.dr;
+			s.sg = s.dg;
+			s.sb = s.db;
+		}
+	}
+}
+
+// Sample construction + material evaluation of Scene::RayTrace (src/scene_trace.cpp:139-452) for the calling lane;
+// the 16 lanes of a half-warp are one 4-quad block. Must be called by all 32 lanes of the warp.
+__device__ __forceinline__ void shade_block(const SceneDev &S, bool sel, const Hit &h, float ox, float oy, float oz, float dx,
+											float dy, float dz, bool packetHasMask, Sample &s) {
+	const int lane = threadIdx.x & 31;
+	const int half = lane >> 4;
+	const int obj = sel ? h.obj : 0;
+
+	s.px = dx * h.dist + ox;
+	s.py = dy * h.dist + oy;
+	s.pz = dz * h.dist + oz;
+	s.dr = s.dg = s.db = s.sr = s.sg = s.sb = 0.0f;
+	s.nx = s.ny = s.nz = 0.0f;
+
+	const unsigned selB = (__ballot_sync(SNL_FULL, sel) >> (half * 16)) & 0xffffu;
+	const int obj0 = __shfl_sync(SNL_FULL, obj, half * 16);
+	const unsigned sameB = (__ballot_sync(SNL_FULL, obj == obj0) >> (half * 16)) & 0xffffu;
+	const bool blockFull = selB == 0xffffu;
+	const bool fast = blockFull && sameB == 0xffffu;
+
+	if(S.gvFull && S.shtris) {
+		int matId = -1;
+		float tu = 0.0f, tv = 0.0f;
+		bool texCoords = false;
+		float4 w0, w1, w2, w3;
+		if(sel) {
+			const float4 *sp = reinterpret_cast<const float4 *>(S.shtris + obj);
+			w0 = __ldg(sp + 0);  // uv0.x uv0.y uv1.x uv1.y
+			w1 = __ldg(sp + 1);  // uv2.x uv2.y n0.x n0.y
+			w2 = __ldg(sp + 2);  // n0.z n1.x n1.y n1.z
+			w3 = __ldg(sp + 3);  // n2.x n2.y n2.z mat
+			const int smat = __float_as_int(w3.w);
+			const int mi = smat & 0x7fffffff;
+			matId = mi < S.nTriMat ? S.triMat[mi] : -1;
+			if(matId >= S.nMats)
+				matId = -1;
+			const bool flat = smat < 0;
+			texCoords = matId >= 0 && (S.mats[matId].flags & 1);
+			const float bx = h.bu, by = h.bv;
+			if(fast && !texCoords) {
+				if(flat) {
+					s.nx = w1.z;
+					s.ny = w1.w;
+					s.nz = w2.x;
+				}
+				else {  // nrm0 + (nrm1 * bar.x + nrm2 * bar.y)   src/scene_trace.cpp:204
+					s.nx = w1.z + (w2.y * bx + w3.x * by);
+					s.ny = w1.w + (w2.z * bx + w3.y * by);
+					s.nz = w2.x + (w2.w * bx + w3.z * by);
+				}
+			}
+			else {  // (nrm0 + nrm1 * bar.x) + nrm2 * bar.y   src/scene_trace.cpp:220,249,275
+				tu = w0.x + w0.z * bx + w1.x * by;
+				tv = w0.y + w0.w * bx + w1.y * by;
+				s.nx = w1.z + w2.y * bx + w3.x * by;
+				s.ny = w1.w + w2.z * bx + w3.y * by;
+				s.nz = w2.x + w2.w * bx + w3.z * by;
+			}
+		}
+		// texDiff: per-quad extent of uv on the single-triangle path, 0 otherwise (src/scene_trace.cpp:219,293-297)
+		float tdx = quad_max(tu) - quad_min(tu), tdy = quad_max(tv) - quad_min(tv);
+		if(!fast) {
+			tdx = 0.0f;
+			tdy = 0.0f;
+		}
+		// which Shade overload runs: fast path keeps the packet's hasMask; the per-lane path is unmasked only when
+		// all 16 lanes hit and share one material (src/scene_trace.cpp:224,302-311,343-345)
+		const int mat0 = __shfl_sync(SNL_FULL, matId, half * 16);
+		const unsigned sameMatB = (__ballot_sync(SNL_FULL, matId == mat0) >> (half * 16)) & 0xffffu;
+		const bool masked = fast ? packetHasMask : !(blockFull && sameMatB == 0xffffu);
+		if(sel)
+			material_shade(S, matId, masked, dx, dy, dz, tu, tv, tdx, tdy, s);
+	}
+	else if(sel) {
+		// simple shading: geometric normal, default material (src/scene_trace.cpp:359-452)
+		const float4 tn = ldg4(&S.gtris[obj].n);
+		s.nx = tn.x;
+		s.ny = tn.y;
+		s.nz = tn.z;
+		material_shade(S, -1, false, dx, dy, dz, 0.0f, 0.0f, 0.0f, 0.0f, s);
+	}
+}
+
+// Scene::TraceLight for one lane (src/scene_trace.cpp:523-601). Returns true when a shadow ray was cast.
+__device__ __forceinline__ bool trace_light(const SceneDev &S, int li, bool sel, const Sample &s, float &ldr, float &ldg,
+											float &ldb, float &lsr, float &lsg, float &lsb, TravCount &tc) {
+	if(!sel)
+		return false;
+	const DevLight &L = S.lights[li];
+	float lx = s.px - L.pos[0], ly = s.py - L.pos[1], lz = s.pz - L.pos[2];
+	if(lx * lx + ly * ly + lz * lz < 0.0001f) {
+		lx = 0.0f;
+		ly = 1.0f;
+		lz = 0.0f;
+	}
+	const float distance = sqrtf(lx * lx + ly * ly + lz * lz);
+	const float inv = 1.0f / distance;
+	const float fx = lx * inv, fy = ly * inv, fz = lz * inv;
+	const float dot = s.nx * fx + s.ny * fy + s.nz * fz;
+	if(!(dot > 0.0f))
+		return false;
+	const float tmax = distance * 0.9999f;
+	const bool occluded = traverse_shadow(S.nodes, S.lightPre[li], L.pos[0], L.pos[1], L.pos[2], fx, fy, fz, safe_inv(fx),
+										  safe_inv(fy), safe_inv(fz), tmax, tc);
+	if(!occluded && tmax > 0.0f) {
+		float atten = distance * L.iRadius;
+		const float x = ((1.0f - atten) * 0.2f + 1.0f / (16.0f * atten * atten)) - 0.0625f;
+		atten = 0.0f > x ? 0.0f : x;  // Max(f32x4(0), x)
+		const float diffMul = dot * atten;
+		float specMul = dot;
+		specMul *= specMul;
+		specMul *= specMul;
+		specMul *= specMul;
+		specMul *= specMul;
+		specMul *= atten;
+		ldr += L.color[0] * diffMul;
+		ldg += L.color[1] * diffMul;
+		ldb += L.color[2] * diffMul;
+		lsr += L.color[0] * specMul;
+		lsg += L.color[1] * specMul;
+		lsb += L.color[2] * specMul;
+	}
+	return true;
+}
+
+struct PacketCounts {
+	unsigned primary, shadow, reflection, reflection_shadow;
+};
+
+// Scene::RayTrace for the calling lane (src/scene_trace.cpp:92-520). LEVEL 0 = the caller's rays, LEVEL 1 = the
+// reflection pass (cache.reflections == 1: no further bounce). All 256 threads of the CTA must call it.
+template <int LEVEL, bool SHARED>
+__device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreTri *__restrict__ originPre, bool active,
+											  bool packetHasMask, float ox, float oy, float oz, float dx, float dy,
+											  float dz, float &outr, float &outg, float &outb, PacketCounts &pc,
+											  TravCount &tc) {
+	Hit h;
+	h.dist = CUDART_INF_F;
+	h.obj = 0;
+	h.bu = h.bv = 0.0f;
+	if(active) {
+		const float ix = safe_inv(dx), iy = safe_inv(dy), iz = safe_inv(dz);
+		if(SHARED)
+			traverse_nearest<true>(S.nodes, originPre, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
+		else
+			traverse_nearest<false>(S.nodes, S.gtris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
+		if(LEVEL == 0)
+			pc.primary++;
+		else
+			pc.reflection++;
+	}
+	__syncwarp();
+
+	if(S.gvDepth) {  // src/scene_trace.cpp:128-137
+		const float dist = active ? (h.dist > CUDART_INF_F ? 0.0f : 1.0f / h.dist) : 0.0f;
+		outr = dist * 20.0f;
+		outg = dist * 250.0f;
+		outb = dist * 2.0f;
+		return;
+	}
+
+	const bool sel = active && h.dist < CUDART_INF_F;
+	Sample s;
+	shade_block(S, sel, h, ox, oy, oz, dx, dy, dz, packetHasMask, s);
+
+	if(LEVEL == 0 && S.gvRefl) {  // src/scene_trace.cpp:454-466, TraceReflection :603-618
+		const bool all = __syncthreads_and(sel);
+		const float dot = s.nx * dx + s.ny * dy + s.nz * dz;
+		const float dd = dot + dot;
+		const float rx = dx - s.nx * dd, ry = dy - s.ny * dd, rz = dz - s.nz * dd;
+		const float rox = s.px + rx * 0.001f, roy = s.py + ry * 0.001f, roz = s.pz + rz * 0.001f;
+		float cr = 0.0f, cg = 0.0f, cb = 0.0f;
+		raytrace_lane<1, false>(S, nullptr, sel, !all, rox, roy, roz, rx, ry, rz, cr, cg, cb, pc, tc);
+		if(sel) {
+			s.dr = s.dr + (cr - s.dr) * 0.3f;
+			s.dg = s.dg + (cg - s.dg) * 0.3f;
+			s.db = s.db + (cb - s.db) * 0.3f;
+		}
+	}
+
+	if(S.nLights) {
+		float ldr = S.ambient[0], ldg = S.ambient[1], ldb = S.ambient[2];
+		float lsr = 0.0f, lsg = 0.0f, lsb = 0.0f;
+		for(int li = 0; li < S.nLights; li++) {
+			const bool cast = trace_light(S, li, sel, s, ldr, ldg, ldb, lsr, lsg, lsb, tc);
+			if(cast) {
+				if(LEVEL == 0)
+					pc.shadow++;
+				else
+					pc.reflection_shadow++;
+			}
+			__syncwarp();
+		}
+		outr = s.dr * ldr + s.sr * lsr;
+		outg = s.dg * ldg + s.sg * lsg;
+		outb = s.db * ldb + s.sb * lsb;
+	}
+	else {
+		outr = s.dr;
+		outg = s.dg;
+		outb = s.db;
+	}
+}
+
+// CTA-level aggregation of the per-lane ray counters into the scene's global counters.
+__device__ __forceinline__ void flush_counts(const SceneDev &S, const PacketCounts &pc, const TravCount &tc) {
+	__shared__ unsigned sh[6];
+	if(threadIdx.x < 6)
+		sh[threadIdx.x] = 0;
+	__syncthreads();
+	unsigned v[6] = {pc.primary, pc.shadow, pc.reflection, pc.reflection_shadow, tc.nodes, tc.tris};
+#pragma unroll
+	for(int i = 0; i < 6; i++) {
+		unsigned x = v[i];
+#pragma unroll
+		for(int o = 16; o; o >>= 1)
+			x += __shfl_xor_sync(SNL_FULL, x, o);
+		if((threadIdx.x & 31) == 0 && x)
+			atomicAdd(&sh[i], x);
+	}
+	__syncthreads();
+	if(threadIdx.x < 6 && sh[threadIdx.x])
+		atomicAdd(reinterpret_cast<unsigned long long *>(S.counters) + threadIdx.x, (unsigned long long)sh[threadIdx.x]);
+}
+
+}  // namespace snl

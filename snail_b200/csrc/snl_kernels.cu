@@ -1,0 +1,238 @@
+// snail_b200 — kernel entry points + launch wrappers (sm_100a). See snl_device.cuh for the device functions.
+#include "snl_device.cuh"
+#include "snl_kernels.h"
+
+namespace snl {
+
+// ---- BVH::TraversePrimary on generated primary rays (snl_trace_primary) -------------------------------------
+// grid = packets (16x16 pixels), block = 256.
+__global__ void __launch_bounds__(kPacket) k_primary(SceneDev S, const PreTri *__restrict__ pre, RayGenParams g, int W, int H,
+												  int packetsX, int *__restrict__ triId, float *__restrict__ t,
+												  float *__restrict__ bary) {
+	const int px0 = (blockIdx.x % packetsX) * 16, py0 = (blockIdx.x / packetsX) * 16;
+	const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+	const int x = px0 + tx, y = py0 + ty;
+	PacketCounts pc = {0, 0, 0, 0};
+	TravCount tc = {0, 0};
+	const bool inside = x < W && y < H;
+	if(inside) {
+		float dx, dy, dz;
+		gen_primary(g, px0, py0, tx, ty, dx, dy, dz);
+		Hit h;
+		h.dist = CUDART_INF_F;
+		h.obj = 0;
+		h.bu = h.bv = 0.0f;
+		traverse_nearest<true>(S.nodes, pre, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, safe_inv(dx), safe_inv(dy),
+							   safe_inv(dz), h, tc);
+		pc.primary = 1;
+		const size_t o = (size_t)y * W + x;
+		const bool hit = h.dist < CUDART_INF_F;
+		if(triId)
+			triId[o] = hit ? h.obj : -1;
+		if(t)
+			t[o] = h.dist;
+		if(bary) {
+			bary[o * 2 + 0] = hit ? h.bu : 0.0f;
+			bary[o * 2 + 1] = hit ? h.bv : 0.0f;
+		}
+	}
+	__syncwarp();
+	flush_counts(S, pc, tc);
+}
+
+// ---- BVH::TraversePrimary on caller rays (snl_trace_rays) ---------------------------------------------------
+template <bool SHARED>
+__global__ void __launch_bounds__(kPacket) k_trace_rays(SceneDev S, const PreTri *__restrict__ pre, const float *__restrict__ o3,
+													 const float *__restrict__ d3, const unsigned char *__restrict__ mask,
+													 int n, int *__restrict__ triId, float *__restrict__ t,
+													 float *__restrict__ bary) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	PacketCounts pc = {0, 0, 0, 0};
+	TravCount tc = {0, 0};
+	if(i < n) {
+		const bool active = !mask || mask[i];
+		Hit h;
+		h.dist = CUDART_INF_F;
+		h.obj = 0;
+		h.bu = h.bv = 0.0f;
+		if(active) {
+			const float *o = SHARED ? o3 : o3 + (size_t)i * 3;
+			const float ox = o[0], oy = o[1], oz = o[2];
+			const float dx = d3[(size_t)i * 3 + 0], dy = d3[(size_t)i * 3 + 1], dz = d3[(size_t)i * 3 + 2];
+			traverse_nearest<SHARED>(S.nodes, SHARED ? (const void *)pre : (const void *)S.gtris, ox, oy, oz, dx, dy, dz,
+									 safe_inv(dx), safe_inv(dy), safe_inv(dz), h, tc);
+			pc.primary = 1;
+		}
+		const bool hit = h.dist < CUDART_INF_F;
+		if(triId)
+			triId[i] = hit ? h.obj : -1;
+		if(t)
+			t[i] = h.dist;
+		if(bary) {
+			bary[(size_t)i * 2 + 0] = hit ? h.bu : 0.0f;
+			bary[(size_t)i * 2 + 1] = hit ? h.bv : 0.0f;
+		}
+	}
+	__syncwarp();
+	flush_counts(S, pc, tc);
+}
+
+// ---- BVH::TraverseShadow on caller rays from one origin (snl_trace_shadow) ----------------------------------
+__global__ void __launch_bounds__(kPacket) k_trace_shadow(SceneDev S, const PreTri *__restrict__ pre, float ox, float oy, float oz,
+													   const float *__restrict__ d3, float *__restrict__ tmax, int n) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	PacketCounts pc = {0, 0, 0, 0};
+	TravCount tc = {0, 0};
+	if(i < n) {
+		const float dist = tmax[i];
+		if(dist >= 0.0f) {
+			const float dx = d3[(size_t)i * 3 + 0], dy = d3[(size_t)i * 3 + 1], dz = d3[(size_t)i * 3 + 2];
+			if(traverse_shadow(S.nodes, pre, ox, oy, oz, dx, dy, dz, safe_inv(dx), safe_inv(dy), safe_inv(dz), dist, tc))
+				tmax[i] = -CUDART_INF_F;
+			pc.shadow = 1;
+		}
+	}
+	__syncwarp();
+	flush_counts(S, pc, tc);
+}
+
+// ---- Scene::RayTrace on caller rays, 256-ray packets (snl_raytrace) -----------------------------------------
+template <bool SHARED>
+__global__ void __launch_bounds__(kPacket) k_raytrace(SceneDev S, const PreTri *__restrict__ pre, const float *__restrict__ o3,
+												   const float *__restrict__ d3, const unsigned char *__restrict__ mask,
+												   int n, float *__restrict__ rgb3) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	// the last packet is padded with masked-off copies of the last ray (a RayGroup always holds whole quads)
+	const int src = i < n ? i : n - 1;
+	// RayGroup<1,0> has no mask (src/ray_group.h:74-160)
+	const bool active = i < n && (SHARED || !mask || mask[i]);
+	const float *o = SHARED ? o3 : o3 + (size_t)src * 3;
+	const float ox = o[0], oy = o[1], oz = o[2];
+	const float dx = d3[(size_t)src * 3 + 0], dy = d3[(size_t)src * 3 + 1], dz = d3[(size_t)src * 3 + 2];
+	const bool all = __syncthreads_and(active);
+	PacketCounts pc = {0, 0, 0, 0};
+	TravCount tc = {0, 0};
+	float r = 0.0f, g = 0.0f, b = 0.0f;
+	raytrace_lane<0, SHARED>(S, pre, active, !SHARED && !all, ox, oy, oz, dx, dy, dz, r, g, b, pc, tc);
+	if(i < n) {
+		rgb3[(size_t)i * 3 + 0] = r;
+		rgb3[(size_t)i * 3 + 1] = g;
+		rgb3[(size_t)i * 3 + 2] = b;
+	}
+	__syncwarp();
+	flush_counts(S, pc, tc);
+}
+
+// ConvColor (src/render.cpp:11-17): trunc(clamp(c * 255, 0, 255)).
+__device__ __forceinline__ unsigned conv_channel(float c) {
+	float v = c * 255.0f;
+	v = v > 0.0f ? v : 0.0f;      // Max(obj, min)
+	v = v < 255.0f ? v : 255.0f;  // Min(.., max)
+	return (unsigned)int(v);
+}
+
+// ---- Render(): RenderTask::Work per packet (src/render.cpp:47-211) ------------------------------------------
+// grid = packets; packet p covers pixels [x0, x0+16) x [y0, y0+16) clipped to (cw, ch). `packets` == null: full image.
+__global__ void __launch_bounds__(kPacket) k_render(SceneDev S, const PreTri *__restrict__ pre, RayGenParams g, int W, int H,
+												 int packetsX, const int4 *__restrict__ packets,
+												 unsigned char *__restrict__ out, size_t pitch) {
+	int px0, py0, cw, ch;
+	if(packets) {
+		const int4 p = packets[blockIdx.x];
+		px0 = p.x;
+		py0 = p.y;
+		cw = p.z;
+		ch = p.w;
+	}
+	else {
+		px0 = (blockIdx.x % packetsX) * 16;
+		py0 = (blockIdx.x / packetsX) * 16;
+		cw = min(16, W - px0);
+		ch = min(16, H - py0);
+	}
+	const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+	float dx, dy, dz;
+	gen_primary(g, px0, py0, tx, ty, dx, dy, dz);
+	PacketCounts pc = {0, 0, 0, 0};
+	TravCount tc = {0, 0};
+	float r = 0.0f, gg = 0.0f, b = 0.0f;
+	// Like the reference we trace the whole 16x16 packet even when it overhangs the image or the tile
+	// (src/render.cpp:112-115): overhanging lanes take part in the 16-lane shading blocks and in the packet-wide
+	// selector.All() test of the reflection pass (src/scene_trace.cpp:615-617), and TreeStats counts them.
+	const bool active = true;
+	raytrace_lane<0, true>(S, pre, active, false, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, r, gg, b, pc, tc);
+	if(S.gvTint) {  // src/render.cpp:118-132
+		r = (r + 0.1f) * S.tint[0];
+		gg = (gg + 0.1f) * S.tint[1];
+		b = (b + 0.1f) * S.tint[2];
+	}
+	if(tx < cw && ty < ch) {
+		unsigned char *dst = out + (size_t)(py0 + ty) * pitch + (size_t)(px0 + tx) * 3;
+		dst[0] = (unsigned char)conv_channel(b);
+		dst[1] = (unsigned char)conv_channel(gg);
+		dst[2] = (unsigned char)conv_channel(r);
+	}
+	__syncwarp();
+	flush_counts(S, pc, tc);
+}
+
+// ---- launch wrappers ------------------------------------------------------------------------------------------
+
+static inline unsigned blocks_for(int n, int per) { return (unsigned)((n + per - 1) / per); }
+
+cudaError_t launch_pretransform(const GenTri *gtris, int nTris, const float origin[3], PreTri *out, cudaStream_t st) {
+	if(nTris <= 0)
+		return cudaSuccess;
+	k_pretransform<<<blocks_for(nTris, 256), 256, 0, st>>>(gtris, nTris, origin[0], origin[1], origin[2], out);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_primary(const SceneDev &S, const PreTri *pre, const RayGenParams &g, int W, int H, int *triId, float *t,
+						   float *bary, cudaStream_t st) {
+	const int px = (W + 15) / 16, py = (H + 15) / 16;
+	k_primary<<<px * py, kPacket, 0, st>>>(S, pre, g, W, H, px, triId, t, bary);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_trace_rays(const SceneDev &S, const PreTri *pre, const float *o3, const float *d3,
+							  const unsigned char *mask, int n, bool shared, int *triId, float *t, float *bary,
+							  cudaStream_t st) {
+	if(n <= 0)
+		return cudaSuccess;
+	if(shared)
+		k_trace_rays<true><<<blocks_for(n, kPacket), kPacket, 0, st>>>(S, pre, o3, d3, mask, n, triId, t, bary);
+	else
+		k_trace_rays<false><<<blocks_for(n, kPacket), kPacket, 0, st>>>(S, pre, o3, d3, mask, n, triId, t, bary);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_trace_shadow(const SceneDev &S, const PreTri *pre, const float origin[3], const float *d3, float *tmax,
+								int n, cudaStream_t st) {
+	if(n <= 0)
+		return cudaSuccess;
+	k_trace_shadow<<<blocks_for(n, kPacket), kPacket, 0, st>>>(S, pre, origin[0], origin[1], origin[2], d3, tmax, n);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_raytrace(const SceneDev &S, const PreTri *pre, const float *o3, const float *d3,
+							const unsigned char *mask, int n, bool shared, float *rgb3, cudaStream_t st) {
+	if(n <= 0)
+		return cudaSuccess;
+	if(shared)
+		k_raytrace<true><<<blocks_for(n, kPacket), kPacket, 0, st>>>(S, pre, o3, d3, mask, n, rgb3);
+	else
+		k_raytrace<false><<<blocks_for(n, kPacket), kPacket, 0, st>>>(S, pre, o3, d3, mask, n, rgb3);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_render(const SceneDev &S, const PreTri *pre, const RayGenParams &g, int W, int H, const int4 *packets,
+						  int nPackets, unsigned char *out, size_t pitch, cudaStream_t st) {
+	const int px = (W + 15) / 16, py = (H + 15) / 16;
+	const int grid = packets ? nPackets : px * py;
+	if(grid <= 0)
+		return cudaSuccess;
+	k_render<<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+	return cudaGetLastError();
+}
+
+}  // namespace snl

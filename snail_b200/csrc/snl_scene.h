@@ -1,0 +1,86 @@
+// snail_b200 — the scene object behind the C ABI handle (host side; owns one device + one stream).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/snail_b200.h"
+#include "snl_device.cuh"
+#include "snl_host_scene.h"
+#include "snl_kernels.h"
+
+namespace snl {
+
+void set_error(const char *fmt, ...);
+
+// cudaMalloc'd array with grow-only capacity.
+template <class T> struct DevBuf {
+	T *ptr = nullptr;
+	size_t cap = 0;
+	cudaError_t reserve(size_t n) {
+		if(n <= cap)
+			return cudaSuccess;
+		if(ptr)
+			cudaFree(ptr);
+		ptr = nullptr;
+		cap = 0;
+		cudaError_t e = cudaMalloc((void **)&ptr, n * sizeof(T));
+		if(e == cudaSuccess)
+			cap = n;
+		return e;
+	}
+	void release() {
+		if(ptr)
+			cudaFree(ptr);
+		ptr = nullptr;
+		cap = 0;
+	}
+};
+
+struct PreCacheEntry {
+	float origin[3];
+	bool valid = false;
+	DevBuf<PreTri> buf;
+};
+
+}  // namespace snl
+
+struct snl_scene {
+	int device = 0;
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	bool evPending = false;
+
+	// reference-layout host copies (kept for snl_scene_copy_host_bvh and re-flattening)
+	snl::HostBVH host;
+	int nTris = 0, nGpuNodes = 0, gpuDepth = 0;
+
+	snl::DevBuf<snl::GpuNode> dNodes;
+	snl::DevBuf<snl::GenTri> dTris;
+	snl::DevBuf<snl::RefShTri> dShTris;
+	bool hasShading = false;
+	snl::DevBuf<int> dTriMat;
+	int nTriMat = 0;
+	snl::DevBuf<snl::DevMaterial> dMats;
+	int nMats = 0;
+	snl::DevBuf<snl::DevTexture> dTexs;
+	std::vector<snl::DevBuf<unsigned char>> dTexData;
+
+	std::vector<snl_light> lights;
+	float ambient[3] = {0.1f, 0.1f, 0.1f};
+	snl::PreCacheEntry lightPre[snl::kMaxLights];
+	snl::PreCacheEntry originPre;  // camera / shared ray origin of the last call
+
+	int gVals[16] = {0};
+
+	snl::DevBuf<snl::Counters> dCounters;
+	snl::DevBuf<unsigned char> dImage;  // staging image for snl_render (host output)
+	snl::DevBuf<unsigned char> dScratch[4];
+	std::vector<int> lastTiles;
+	snl::DevBuf<int4> dPackets;
+	int nPackets = 0;
+
+	uint64_t launches = 0;
+};
