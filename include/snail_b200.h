@@ -128,6 +128,21 @@ int snl_set_options(snl_scene *, const int gVals[16]);
 int snl_scene_load_obj(snl_scene *, const char *objPath, const char *mtlPath, const char *texDir,
 					   int flipNormalsFlag, int buildFlags);
 
+/* The same host ingest + builder without a device (host logic only; usable on a machine with no GPU), and the
+ * hand-over of its result to a scene (= the flatten + upload step of snl_scene_load_obj). */
+typedef struct snl_host_scene snl_host_scene;
+snl_host_scene *snl_host_scene_load_obj(const char *objPath, const char *mtlPath, const char *texDir,
+										int flipNormalsFlag, int buildFlags);
+void snl_host_scene_free(snl_host_scene *);
+int snl_host_scene_counts(const snl_host_scene *, int *nNodes, int *nTris, int *nMatIds, int *depth, int *nMaterials,
+						  int *nTextures);
+/* reference layouts: BVH::Node[nNodes], Triangle[nTris], ShTriangle[nTris] (untouched when built with
+ * noShadingData), BVH::materials[i].id */
+int snl_host_scene_copy(const snl_host_scene *, void *nodes, void *tris, void *shTris, int *triMatId);
+int snl_host_scene_material(const snl_host_scene *, int idx, snl_material *out);
+int snl_host_scene_texture(const snl_host_scene *, int idx, snl_texture *out); /* out->data stays owned by the handle */
+int snl_scene_set_host_scene(snl_scene *, const snl_host_scene *);
+
 /* Read back what the host builder produced (reference layouts, for parity checks against the reference's
  * BVH::nodes/tris/shTris). Any out pointer may be NULL. */
 int snl_scene_counts(snl_scene *, int *nNodes, int *nTris, int *nMatIds, int *depth, int *nMaterials);

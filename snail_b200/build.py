@@ -1,0 +1,64 @@
+"""Builds snail_b200/libsnail_b200.so in-tree with nvcc for sm_100a (cross-compiles without a GPU).
+
+`python -m snail_b200.build [--counters] [--force]`
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libsnail_b200.so")
+LIB_COUNTERS = os.path.join(HERE, "libsnail_b200_counters.so")
+
+SOURCES = ["snl_kernels.cu", "snl_capi.cu", "snl_host_scene.cpp"]
+HEADERS = ["snl_device.cuh", "snl_kernels.h", "snl_scene.h", "snl_scene_dev.h", "snl_types.h", "snl_host_scene.h",
+           os.path.join("..", "..", "include", "snail_b200.h")]
+
+# -fmad=false / -ffp-contract=off: every float expression keeps the reference's operation order and rounding,
+# which is what makes hit records bit-identical to the reference built on veclib's scalar back-end.
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
+              "-Xcompiler", "-fPIC,-ffp-contract=off,-O2", "--use_fast_math=false"]
+
+
+def _nvcc() -> str:
+    for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and os.path.exists(cand):
+            return cand
+    raise RuntimeError("nvcc not found")
+
+
+def _stale(target: str) -> bool:
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS] + [os.path.abspath(__file__)]
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build_library(force: bool = False, counters: bool = False, verbose: bool = False) -> str:
+    target = LIB_COUNTERS if counters else LIB
+    if not force and not _stale(target):
+        return target
+    flags = [f for f in NVCC_FLAGS if f != "--use_fast_math=false"]
+    if counters:
+        flags += ["-DSNL_COUNTERS"]
+    if verbose:
+        flags += ["-Xptxas", "-v"]
+    cmd = [_nvcc(), "-shared", *flags, "-I", os.path.join(HERE, "..", "include"),
+           *[os.path.join(CSRC, s) for s in SOURCES], "-o", target + ".tmp", "-lz"]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + res.stdout + res.stderr)
+    if verbose:
+        print(res.stderr)
+    os.replace(target + ".tmp", target)
+    return target
+
+
+if __name__ == "__main__":
+    path = build_library(force="--force" in sys.argv, counters="--counters" in sys.argv, verbose="-v" in sys.argv)
+    print(path)

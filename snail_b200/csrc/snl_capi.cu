@@ -506,11 +506,13 @@ uint64_t snl_scene_stream(snl_scene *s) { return s ? (uint64_t)(uintptr_t)s->str
 
 // ---- compute entry points ---------------------------------------------------------------------------------------
 
+}  // extern "C"
 template <class T> static int scratch(snl_scene *s, int slot, size_t count, T **out) {
 	SNL_CUDA(s->dScratch[slot].reserve(std::max<size_t>(count * sizeof(T), 16)));
 	*out = reinterpret_cast<T *>(s->dScratch[slot].ptr);
 	return SNL_OK;
 }
+extern "C" {
 
 #define SNL_TRY(expr)    \
 	do {                 \
@@ -721,17 +723,9 @@ int snl_render(snl_scene *s, const snl_camera *cam, int W, int H, const int *til
 	return sync_and_stats(s, stats);
 }
 
-int snl_scene_load_obj(snl_scene *s, const char *objPath, const char *mtlPath, const char *texDir, int flipNormalsFlag,
-					   int buildFlags) {
-	SNL_REQUIRE(s && objPath, SNL_ERR_INVALID, "null argument");
+static int set_host_scene(snl_scene *s, const HostScene &hs) {
 	SNL_CUDA(cudaSetDevice(s->device));
-	HostScene hs;
-	std::string err;
-	if(!load_obj_scene(objPath, mtlPath, texDir, flipNormalsFlag, buildFlags, hs, err)) {
-		set_error("%s", err.c_str());
-		return SNL_ERR_IO;
-	}
-	s->host = std::move(hs.bvh);
+	s->host = hs.bvh;
 	SNL_TRY(upload_geometry(s));
 	std::vector<snl_material> mats;
 	for(auto &m : hs.mats)
@@ -740,6 +734,87 @@ int snl_scene_load_obj(snl_scene *s, const char *objPath, const char *mtlPath, c
 	for(auto &t : hs.texs)
 		texs.push_back(snl_texture{t.data.data(), t.data.size(), t.width, t.height, t.mips});
 	return upload_materials(s, mats.data(), (int)mats.size(), texs.data(), (int)texs.size());
+}
+
+snl_host_scene *snl_host_scene_load_obj(const char *objPath, const char *mtlPath, const char *texDir, int flipNormalsFlag,
+										int buildFlags) {
+	if(!objPath) {
+		set_error("null path");
+		return nullptr;
+	}
+	snl_host_scene *h = new snl_host_scene;
+	std::string err;
+	if(!load_obj_scene(objPath, mtlPath, texDir, flipNormalsFlag, buildFlags, h->scene, err)) {
+		set_error("%s", err.c_str());
+		delete h;
+		return nullptr;
+	}
+	return h;
+}
+
+void snl_host_scene_free(snl_host_scene *h) { delete h; }
+
+int snl_host_scene_counts(const snl_host_scene *h, int *nNodes, int *nTris, int *nMatIds, int *depth, int *nMaterials,
+						  int *nTextures) {
+	SNL_REQUIRE(h, SNL_ERR_INVALID, "null handle");
+	const HostBVH &b = h->scene.bvh;
+	if(nNodes)
+		*nNodes = (int)b.nodes.size();
+	if(nTris)
+		*nTris = (int)b.tris.size();
+	if(nMatIds)
+		*nMatIds = (int)b.triMatId.size();
+	if(depth)
+		*depth = b.depth;
+	if(nMaterials)
+		*nMaterials = (int)h->scene.mats.size();
+	if(nTextures)
+		*nTextures = (int)h->scene.texs.size();
+	return SNL_OK;
+}
+
+int snl_host_scene_copy(const snl_host_scene *h, void *nodes, void *tris, void *shTris, int *triMatId) {
+	SNL_REQUIRE(h, SNL_ERR_INVALID, "null handle");
+	const HostBVH &b = h->scene.bvh;
+	if(nodes)
+		memcpy(nodes, b.nodes.data(), b.nodes.size() * sizeof(RefNode));
+	if(tris)
+		memcpy(tris, b.tris.data(), b.tris.size() * sizeof(RefTriangle));
+	if(shTris)
+		memcpy(shTris, b.shTris.data(), b.shTris.size() * sizeof(RefShTri));
+	if(triMatId)
+		memcpy(triMatId, b.triMatId.data(), b.triMatId.size() * sizeof(int));
+	return SNL_OK;
+}
+
+int snl_host_scene_material(const snl_host_scene *h, int idx, snl_material *out) {
+	SNL_REQUIRE(h && out && idx >= 0 && idx < (int)h->scene.mats.size(), SNL_ERR_INVALID, "bad argument");
+	*out = h->scene.mats[idx].m;
+	return SNL_OK;
+}
+
+int snl_host_scene_texture(const snl_host_scene *h, int idx, snl_texture *out) {
+	SNL_REQUIRE(h && out && idx >= 0 && idx < (int)h->scene.texs.size(), SNL_ERR_INVALID, "bad argument");
+	const HostTexture &t = h->scene.texs[idx];
+	*out = snl_texture{t.data.data(), t.data.size(), t.width, t.height, t.mips};
+	return SNL_OK;
+}
+
+int snl_scene_set_host_scene(snl_scene *s, const snl_host_scene *h) {
+	SNL_REQUIRE(s && h, SNL_ERR_INVALID, "null argument");
+	return set_host_scene(s, h->scene);
+}
+
+int snl_scene_load_obj(snl_scene *s, const char *objPath, const char *mtlPath, const char *texDir, int flipNormalsFlag,
+					   int buildFlags) {
+	SNL_REQUIRE(s && objPath, SNL_ERR_INVALID, "null argument");
+	HostScene hs;
+	std::string err;
+	if(!load_obj_scene(objPath, mtlPath, texDir, flipNormalsFlag, buildFlags, hs, err)) {
+		set_error("%s", err.c_str());
+		return SNL_ERR_IO;
+	}
+	return set_host_scene(s, hs);
 }
 
 }  // extern "C"

@@ -9,29 +9,11 @@
 #include <cuda_runtime.h>
 #include <math_constants.h>
 
-#include "snl_types.h"
+#include "snl_scene_dev.h"
 
 namespace snl {
 
 #define SNL_FULL 0xffffffffu
-
-enum { kStack = 96, kPacket = 256 };
-
-struct SceneDev {
-	const GpuNode *nodes;
-	const GenTri *gtris;
-	const RefShTri *shtris;  // null: no shading data (BVH::noShadingData)
-	const int *triMat;       // BVH::materials[i].id
-	const DevMaterial *mats;
-	const DevTexture *texs;
-	const PreTri *lightPre[kMaxLights];
-	DevLight lights[kMaxLights];
-	int nTriMat, nMats, nLights;
-	float ambient[3];
-	int gvDepth, gvFull, gvRefl, gvTint;  // gVals[1], [6], [7], [8]
-	float tint[3];
-	Counters *counters;
-};
 
 __device__ __forceinline__ float4 ldg4(const Float4 *p) { return __ldg(reinterpret_cast<const float4 *>(p)); }
 __device__ __forceinline__ int4 ldg4(const Int4 *p) { return __ldg(reinterpret_cast<const int4 *>(p)); }
@@ -222,33 +204,6 @@ __device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ node
 		cur = stack[--sp];
 	}
 	return false;
-}
-
-// Triangle::Collide sharedOrigin precomputation (src/triangle.cpp:9-18) for every triangle and one origin.
-__global__ void __launch_bounds__(256) k_pretransform(const GenTri *__restrict__ gtris, int nTris, float ox, float oy,
-													 float oz, PreTri *__restrict__ out) {
-	const int i = blockIdx.x * blockDim.x + threadIdx.x;
-	if(i >= nTris)
-		return;
-	const float4 ta = ldg4(&gtris[i].a), tba = ldg4(&gtris[i].ba), tca = ldg4(&gtris[i].ca), tn = ldg4(&gtris[i].n);
-	const float it0 = ta.w;
-	const float tx = ox - ta.x, ty = oy - ta.y, tz = oz - ta.z;
-	float4 u, v, n;
-	// tvec0 = (ba ^ tvec) * it0
-	v.x = (tba.y * tz - tba.z * ty) * it0;
-	v.y = (tba.z * tx - tba.x * tz) * it0;
-	v.z = (tba.x * ty - tba.y * tx) * it0;
-	v.w = 0.0f;
-	// tvec1 = (tvec ^ ca) * it0
-	u.x = (ty * tca.z - tz * tca.y) * it0;
-	u.y = (tz * tca.x - tx * tca.z) * it0;
-	u.z = (tx * tca.y - ty * tca.x) * it0;
-	u.w = -(tx * tn.x + ty * tn.y + tz * tn.z);
-	n = make_float4(tn.x, tn.y, tn.z, 0.0f);
-	float4 *o = reinterpret_cast<float4 *>(out + i);
-	o[0] = u;
-	o[1] = v;
-	o[2] = n;
 }
 
 // SafeInv (src/rtbase.h:117-119): Inv(v + 1e-8).

@@ -4,6 +4,33 @@
 
 namespace snl {
 
+// Triangle::Collide sharedOrigin precomputation (src/triangle.cpp:9-18) for every triangle and one origin.
+__global__ void __launch_bounds__(256) k_pretransform(const GenTri *__restrict__ gtris, int nTris, float ox, float oy,
+													 float oz, PreTri *__restrict__ out) {
+	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i >= nTris)
+		return;
+	const float4 ta = ldg4(&gtris[i].a), tba = ldg4(&gtris[i].ba), tca = ldg4(&gtris[i].ca), tn = ldg4(&gtris[i].n);
+	const float it0 = ta.w;
+	const float tx = ox - ta.x, ty = oy - ta.y, tz = oz - ta.z;
+	float4 u, v, n;
+	// tvec0 = (ba ^ tvec) * it0
+	v.x = (tba.y * tz - tba.z * ty) * it0;
+	v.y = (tba.z * tx - tba.x * tz) * it0;
+	v.z = (tba.x * ty - tba.y * tx) * it0;
+	v.w = 0.0f;
+	// tvec1 = (tvec ^ ca) * it0
+	u.x = (ty * tca.z - tz * tca.y) * it0;
+	u.y = (tz * tca.x - tx * tca.z) * it0;
+	u.z = (tx * tca.y - ty * tca.x) * it0;
+	u.w = -(tx * tn.x + ty * tn.y + tz * tn.z);
+	n = make_float4(tn.x, tn.y, tn.z, 0.0f);
+	float4 *o = reinterpret_cast<float4 *>(out + i);
+	o[0] = u;
+	o[1] = v;
+	o[2] = n;
+}
+
 // ---- BVH::TraversePrimary on generated primary rays (snl_trace_primary) -------------------------------------
 // grid = packets (16x16 pixels), block = 256.
 __global__ void __launch_bounds__(kPacket) k_primary(SceneDev S, const PreTri *__restrict__ pre, RayGenParams g, int W, int H,

@@ -7,7 +7,7 @@
 #include <vector>
 
 #include "../../include/snail_b200.h"
-#include "snl_device.cuh"
+#include "snl_scene_dev.h"
 #include "snl_host_scene.h"
 #include "snl_kernels.h"
 
@@ -46,6 +46,10 @@ struct PreCacheEntry {
 };
 
 }  // namespace snl
+
+struct snl_host_scene {
+	snl::HostScene scene;
+};
 
 struct snl_scene {
 	int device = 0;
