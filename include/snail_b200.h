@@ -86,7 +86,8 @@ typedef struct snl_stats {
 	uint64_t reflection;
 	uint64_t reflection_shadow;
 	uint64_t node_visits;   /* only counted when the library is built with SNL_COUNTERS */
-	uint64_t tri_tests;     /* idem */
+	uint64_t tri_tests;     /* idem: 48-byte per-origin triangle records tested */
+	uint64_t gtri_tests;    /* idem: 64-byte general triangle records tested (reflection rays) */
 	float kernel_ms;        /* device time of the last call's kernels (CUDA events on the scene's stream) */
 } snl_stats;
 

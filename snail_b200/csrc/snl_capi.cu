@@ -153,6 +153,7 @@ int sync_and_stats(snl_scene *s, snl_stats *stats) {
 		stats->rays = c.primary + c.shadow + c.reflection + c.reflection_shadow;
 		stats->node_visits = c.node_visits;
 		stats->tri_tests = c.tri_tests;
+		stats->gtri_tests = c.gtri_tests;
 		if(s->evPending) {
 			float ms = 0.0f;
 			if(cudaEventElapsedTime(&ms, s->ev0, s->ev1) == cudaSuccess)

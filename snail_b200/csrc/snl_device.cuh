@@ -25,7 +25,7 @@ __device__ __forceinline__ int4 ldg4(const Int4 *p) { return __ldg(reinterpret_c
 #endif
 
 struct TravCount {
-	unsigned nodes, tris;
+	unsigned nodes, tris, gtris;  // inner nodes fetched, PreTri records tested, GenTri records tested
 };
 
 // BBox::Test, one ray vs one box (src/bounding_box.cpp:61-97): hit <=> lmax >= 0 && lmin <= min(lmax, dist).
@@ -137,7 +137,10 @@ __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nod
 			const int leaf = ~cur;
 			const int first = leaf & kLeafFirstMask, count = (leaf >> kLeafFirstBits) + 1;
 			for(int i = 0; i < count; i++) {
-				SNL_COUNT(tc.tris);
+				if(SHARED)
+					SNL_COUNT(tc.tris);
+				else
+					SNL_COUNT(tc.gtris);
 				if(SHARED)
 					tri_nearest_pre(reinterpret_cast<const PreTri *>(tris) + first + i, first + i, dx, dy, dz, h);
 				else
@@ -540,13 +543,13 @@ __device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreTri *_
 
 // CTA-level aggregation of the per-lane ray counters into the scene's global counters.
 __device__ __forceinline__ void flush_counts(const SceneDev &S, const PacketCounts &pc, const TravCount &tc) {
-	__shared__ unsigned sh[6];
-	if(threadIdx.x < 6)
+	__shared__ unsigned sh[7];
+	if(threadIdx.x < 7)
 		sh[threadIdx.x] = 0;
 	__syncthreads();
-	unsigned v[6] = {pc.primary, pc.shadow, pc.reflection, pc.reflection_shadow, tc.nodes, tc.tris};
+	unsigned v[7] = {pc.primary, pc.shadow, pc.reflection, pc.reflection_shadow, tc.nodes, tc.tris, tc.gtris};
 #pragma unroll
-	for(int i = 0; i < 6; i++) {
+	for(int i = 0; i < 7; i++) {
 		unsigned x = v[i];
 #pragma unroll
 		for(int o = 16; o; o >>= 1)
@@ -555,7 +558,7 @@ __device__ __forceinline__ void flush_counts(const SceneDev &S, const PacketCoun
 			atomicAdd(&sh[i], x);
 	}
 	__syncthreads();
-	if(threadIdx.x < 6 && sh[threadIdx.x])
+	if(threadIdx.x < 7 && sh[threadIdx.x])
 		atomicAdd(reinterpret_cast<unsigned long long *>(S.counters) + threadIdx.x, (unsigned long long)sh[threadIdx.x]);
 }
 

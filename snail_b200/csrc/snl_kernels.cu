@@ -40,7 +40,7 @@ __global__ void __launch_bounds__(kPacket) k_primary(SceneDev S, const PreTri *_
 	const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
 	const int x = px0 + tx, y = py0 + ty;
 	PacketCounts pc = {0, 0, 0, 0};
-	TravCount tc = {0, 0};
+	TravCount tc = {0, 0, 0};
 	const bool inside = x < W && y < H;
 	if(inside) {
 		float dx, dy, dz;
@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(kPacket) k_trace_rays(SceneDev S, const PreTri
 													 float *__restrict__ bary) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	PacketCounts pc = {0, 0, 0, 0};
-	TravCount tc = {0, 0};
+	TravCount tc = {0, 0, 0};
 	if(i < n) {
 		const bool active = !mask || mask[i];
 		Hit h;
@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(kPacket) k_trace_shadow(SceneDev S, const PreT
 													   const float *__restrict__ d3, float *__restrict__ tmax, int n) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	PacketCounts pc = {0, 0, 0, 0};
-	TravCount tc = {0, 0};
+	TravCount tc = {0, 0, 0};
 	if(i < n) {
 		const float dist = tmax[i];
 		if(dist >= 0.0f) {
@@ -138,7 +138,7 @@ __global__ void __launch_bounds__(kPacket) k_raytrace(SceneDev S, const PreTri *
 	const float dx = d3[(size_t)src * 3 + 0], dy = d3[(size_t)src * 3 + 1], dz = d3[(size_t)src * 3 + 2];
 	const bool all = __syncthreads_and(active);
 	PacketCounts pc = {0, 0, 0, 0};
-	TravCount tc = {0, 0};
+	TravCount tc = {0, 0, 0};
 	float r = 0.0f, g = 0.0f, b = 0.0f;
 	raytrace_lane<0, SHARED>(S, pre, active, !SHARED && !all, ox, oy, oz, dx, dy, dz, r, g, b, pc, tc);
 	if(i < n) {
@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(kPacket) k_render(SceneDev S, const PreTri *__
 	float dx, dy, dz;
 	gen_primary(g, px0, py0, tx, ty, dx, dy, dz);
 	PacketCounts pc = {0, 0, 0, 0};
-	TravCount tc = {0, 0};
+	TravCount tc = {0, 0, 0};
 	float r = 0.0f, gg = 0.0f, b = 0.0f;
 	// Like the reference we trace the whole 16x16 packet even when it overhangs the image or the tile
 	// (src/render.cpp:112-115): overhanging lanes take part in the 16-lane shading blocks and in the packet-wide

@@ -114,7 +114,7 @@ struct RayGenParams {
 };
 
 struct Counters {
-	unsigned long long primary, shadow, reflection, reflection_shadow, node_visits, tri_tests;
+	unsigned long long primary, shadow, reflection, reflection_shadow, node_visits, tri_tests, gtri_tests;
 };
 
 }  // namespace snl
