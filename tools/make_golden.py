@@ -1,0 +1,123 @@
+#!/usr/bin/env python
+"""TEST INFRASTRUCTURE — generates tests/golden/*.npz + tests/golden/manifest.json from the reference itself.
+
+The reference (nadult/Snail) ships no golden vectors or known-answer tests for its tracing path, so
+the goldens are OUTPUTS OF THE REFERENCE RUN HERE: oracle/_ref/libsnailref_scalar.so is the unmodified reference
+hot path compiled in place from /root/reference by oracle/build_ref.sh on veclib's scalar back-end (exact 1/x and
+1/sqrt, so the numbers do not depend on the host's rcpps/rsqrtps tables). Re-run with
+
+    bash oracle/build_ref.sh && python tools/make_golden.py
+
+Each case stores: the camera, the light, W, H, the per-pixel nearest hit {triId, t, bary} of
+BVH::TraversePrimary, the BGR8 frame of Render() for every gVals stage, TreeStats ray counts, a set of incoherent
+rays with their hits, a set of shadow rays with their verdicts, and sha256 digests of the builder's output
+(BVH::nodes / tris / shTris) so that the host ingest + SAH builder can be pinned without the oracle.
+"""
+from __future__ import annotations
+
+import hashlib
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import snailref as R  # noqa: E402
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+SCENES = os.path.join(ROOT, "oracle", "_ref", "scenes")
+TEXDIR = os.path.join(ROOT, "oracle", "_ref", "data") + "/"
+DATA = os.path.join(ROOT, "data")
+
+STAGES = {
+    "simple_nolight": ({}, False),
+    "depth": ({1: 1}, False),
+    "simple_light": ({}, True),
+    "full_light": ({6: 1}, True),
+    "whitted": ({6: 1, 7: 1}, True),
+}
+
+# name -> (obj, mtl, inside camera, W, H)
+CASES = {
+    "box": ("box.obj", None, True, 96, 80),
+    "lancia": ("lancia.obj", None, False, 128, 80),
+    "feline": ("feline.obj", None, False, 128, 80),
+    "barracks_tex": ("barracks.obj", "barracks.mtl", False, 128, 80),
+}
+
+
+def random_rays(n, bmin, bmax, seed):
+    rng = np.random.default_rng(seed)
+    c = (bmin + bmax) * 0.5
+    ext = bmax - bmin
+    o = (c + (rng.random((n, 3)) - 0.5) * ext * 2.5).astype(np.float32)
+    target = (c + (rng.random((n, 3)) - 0.5) * ext).astype(np.float32)
+    d = target - o
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    return o, d.astype(np.float32)
+
+
+def sha(a: np.ndarray) -> str:
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def main():
+    os.makedirs(GOLDEN, exist_ok=True)
+    manifest = {"generator": "tools/make_golden.py", "oracle": "oracle/_ref/libsnailref_scalar.so (reference compiled in place)",
+                "backend": R.lib("scalar").ref_backend().decode(), "cases": {}}
+    for name, (obj, mtl, inside, W, H) in CASES.items():
+        mtl_path = os.path.join(DATA, mtl) if mtl else None
+        ref = R.RefScene(os.path.join(SCENES, obj), mtl_path, TEXDIR if mtl else "", variant="scalar")
+        bmin, bmax = ref.bbox()
+        cam, light = R.bench_camera(bmin, bmax, inside=inside)
+        out = {"camera": cam, "light": light, "size": np.array([W, H], np.int32)}
+        ref.set_gvals({})
+        ref.set_lights([])
+        tri, t, bary = ref.trace_primary(cam, W, H)
+        out["tri"], out["t"], out["bary"] = tri, t, bary
+        out["dirs"] = ref.primary_dirs(cam, W, H)
+        rays = {}
+        for stage, (gv, lit) in STAGES.items():
+            ref.set_gvals(gv)
+            ref.set_lights([light] if lit else [])
+            img, st, _ = ref.render(cam, W, H, threads=1)
+            out["img_" + stage] = img
+            rays[stage] = st["rays"]
+        # incoherent rays with their own origins (Context<0,0> / <0,1>)
+        n = 256 * 3 + 77
+        o, d = random_rays(n, bmin, bmax, 7)
+        mask = (np.arange(n) % 5 != 0).astype(np.uint8)
+        out["ray_o"], out["ray_d"], out["ray_mask"] = o, d, mask
+        out["ray_tri"], out["ray_t"], out["ray_bary"] = ref.trace_rays(o, d, None)
+        out["rayM_tri"], out["rayM_t"], out["rayM_bary"] = ref.trace_rays(o, d, mask)
+        # shadow rays from one origin (ShadowContext)
+        origin = ((bmin + bmax) * 0.5).astype(np.float32) if inside else \
+            ((bmin + bmax) * 0.5 + np.float32([0.3, 0.5, -1]) * np.linalg.norm(bmax - bmin)).astype(np.float32)
+        rng = np.random.default_rng(5)
+        tmax = (rng.random(n) * 3 * np.linalg.norm(bmax - bmin)).astype(np.float32)
+        tmax[::7] = -1.0
+        out["sh_origin"], out["sh_tmax"] = origin, tmax
+        out["sh_out"] = ref.trace_shadow(origin, d, tmax)
+        # Scene::RayTrace on caller packets (RayGroup<0,0>), Whitted
+        ref.set_gvals({6: 1, 7: 1})
+        ref.set_lights([light])
+        out["rt_rgb"], rt_rays = ref.raytrace(o, d, None)
+        nodes, tris, shtris = ref.nodes(), ref.tris(), ref.shtris()
+        np.savez_compressed(os.path.join(GOLDEN, name + ".npz"), **out)
+        manifest["cases"][name] = {
+            "obj": obj, "mtl": mtl, "inside": inside, "W": W, "H": H, "rays": rays, "raytrace_rays": rt_rays,
+            "n_nodes": int(ref.n_nodes), "n_tris": int(ref.n_tris), "depth": int(ref.depth),
+            "sha256_nodes": sha(nodes), "sha256_tris": sha(tris), "sha256_shtris": sha(shtris),
+            "matids": [int(x) for x in ref.matids()],
+            "hits": int((tri >= 0).sum()),
+        }
+        print(name, manifest["cases"][name]["hits"], "hits of", W * H, "rays:", rays)
+        ref.close()
+    with open(os.path.join(GOLDEN, "manifest.json"), "w") as f:
+        json.dump(manifest, f, indent=1, sort_keys=True)
+
+
+if __name__ == "__main__":
+    main()
