@@ -464,13 +464,133 @@ struct Builder {
 		split(subNode + 0, first, minIdx, sdepth + 1);
 		split(subNode + 1, first + minIdx, count - minIdx, sdepth + 1);
 	}
+
+	// BVH::FindSplit (src/bvh/tree.cpp:161-287), the fastBuild path: 16 centroid bins along the widest axis of the
+	// node box, SAH over the 15 bin boundaries, std::partition of the triangle range. Leaves keep the box their parent
+	// gave them (no refit), and there is no depth cap here.
+	enum { nBins = 16 };
+	static int bin_of(float centre, float sub, float mul) {
+		const float f = (centre - sub) * mul;
+		// a degenerate node box makes mul inf/NaN; the reference indexes out of bounds there (UB) — we clamp
+		if(!(f >= 0.0f))
+			return 0;
+		return f >= float(nBins) ? nBins - 1 : int(f);
+	}
+	void split_binned(int nNode, int first, int count, int sdepth) {
+		std::vector<RefTriangle> &tris = bvh.tris;
+		const Box bbox = get_box(nNode);
+		auto leaf = [&]() {
+			bvh.depth = std::max(bvh.depth, sdepth);
+			bvh.nodes[nNode].sub = (int32_t)(first | 0x80000000u);
+			bvh.nodes[nNode].count = count;
+		};
+		if(count <= 4) {
+			leaf();
+			return;
+		}
+		const int axis = max_axis(bbox.mx[0] - bbox.mn[0], bbox.mx[1] - bbox.mn[1], bbox.mx[2] - bbox.mn[2]);
+		const float inf = std::numeric_limits<float>::infinity();
+		Box binBox[nBins];
+		int binCount[nBins];
+		for(int n = 0; n < nBins; n++) {
+			binCount[n] = 0;
+			for(int a = 0; a < 3; a++) {
+				binBox[n].mn[a] = inf;
+				binBox[n].mx[a] = -inf;
+			}
+		}
+		const float mul = nBins * (1.0f - 0.0001f) / (bbox.mx[axis] - bbox.mn[axis]);  // constant::epsilon, veclib/vecbase.h:40
+		const float sub = bbox.mn[axis];
+		for(int n = 0; n < count; n++) {
+			const Box b = tri_box(tris[first + n]);
+			const int bin = bin_of((b.mx[axis] + b.mn[axis]) * 0.5f, sub, mul);
+			binCount[bin]++;
+			box_add(binBox[bin], b);
+		}
+		Box lBox[nBins], rBox[nBins];
+		int lCnt[nBins], rCnt[nBins];
+		lBox[0] = binBox[0];
+		lCnt[0] = binCount[0];
+		for(int n = 1; n < nBins; n++) {
+			lBox[n] = lBox[n - 1];
+			box_add(lBox[n], binBox[n]);
+			lCnt[n] = lCnt[n - 1] + binCount[n];
+		}
+		rBox[nBins - 1] = binBox[nBins - 1];
+		rCnt[nBins - 1] = binCount[nBins - 1];
+		for(int n = nBins - 2; n >= 0; n--) {
+			rBox[n] = rBox[n + 1];
+			box_add(rBox[n], binBox[n]);
+			rCnt[n] = rCnt[n + 1] + binCount[n];
+		}
+		float minCost = inf;
+		const float noSplitCost = 1.0f * count * box_sa(bbox);
+		int minIdx = 1;
+		for(int n = 1; n < nBins; n++) {
+			const float cost = (lCnt[n - 1] ? box_sa(lBox[n - 1]) * lCnt[n - 1] : 0) + (rCnt[n] ? box_sa(rBox[n]) * rCnt[n] : 0);
+			if(cost < minCost) {
+				minCost = cost;
+				minIdx = n;
+			}
+		}
+		minCost = 0.0f + 1.0f * minCost;
+		if(noSplitCost < minCost) {
+			leaf();
+			return;
+		}
+		std::vector<int> indices(count);
+		for(int n = 0; n < count; n++)
+			indices[n] = first + n;
+		// TestTris (src/bvh/tree.cpp:24-43): centre from the three vertices' own min/max
+		std::partition(&indices[0], &indices[0] + count, [&](int idx) {
+			const RefTriangle &t = tris[idx];
+			const float f1 = t.a[axis], f2 = t.ba[axis] + t.a[axis], f3 = t.ca[axis] + t.a[axis];
+			const float centre = (fmin2(f1, fmin2(f2, f3)) + fmax2(f1, fmax2(f2, f3))) * 0.5f;
+			return int((centre - sub) * mul) < minIdx;
+		});
+		reorder(indices, first, count);
+		Box leftBox = lBox[minIdx - 1], rightBox = rBox[minIdx];
+		int leftCount = lCnt[minIdx - 1], rightCount = rCnt[minIdx];
+		if(leftCount == 0 || rightCount == 0) {
+			minIdx = count / 2;
+			leftBox = tri_box(tris[first]);
+			rightBox = tri_box(tris[first + count - 1]);
+			for(int n = 1; n < minIdx; n++)
+				box_add(leftBox, tri_box(tris[first + n]));
+			for(int n = minIdx; n < count; n++)
+				box_add(rightBox, tri_box(tris[first + n]));
+			leftCount = minIdx;
+			rightCount = count - leftCount;
+		}
+		const int subNode = (int)bvh.nodes.size();
+		bvh.nodes[nNode].sub = subNode;
+		bvh.nodes[nNode].axis = (int16_t)axis;
+		bvh.nodes[nNode].firstNode =
+			leftBox.mn[axis] == rightBox.mn[axis] ? (leftBox.mx[axis] < rightBox.mx[axis] ? 0 : 1) : 0;
+		push_node(leftBox);
+		push_node(rightBox);
+		split_binned(subNode + 0, first, leftCount, sdepth + 1);
+		split_binned(subNode + 1, first + leftCount, rightCount, sdepth + 1);
+	}
+
+	// applies a permutation of [first, first + count) to tris (and shTris)
+	void reorder(const std::vector<int> &indices, int first, int count) {
+		std::vector<RefTriangle> ttemp(count);
+		for(int n = 0; n < count; n++)
+			ttemp[n] = bvh.tris[indices[n]];
+		for(int n = 0; n < count; n++)
+			bvh.tris[first + n] = ttemp[n];
+		if(!bvh.shTris.empty()) {
+			std::vector<RefShTri> stemp(count);
+			for(int n = 0; n < count; n++)
+				stemp[n] = bvh.shTris[indices[n]];
+			for(int n = 0; n < count; n++)
+				bvh.shTris[first + n] = stemp[n];
+		}
+	}
 };
 
 bool build_bvh(const Object &obj, const std::map<std::string, int> &matNames, int flags, HostBVH &bvh, std::string &err) {
-	if(flags & kFastBuild) {
-		err = "BVH::fastBuild (16-bin FindSplit, src/bvh/tree.cpp:161-287) is not implemented; use useSah (4) or 0";
-		return false;
-	}
 	bvh = HostBVH();
 	to_tri_vectors(obj, !(flags & kNoShadingData), bvh.tris, bvh.shTris);
 	bvh.nodes.reserve(bvh.tris.size() * 2);
@@ -479,7 +599,10 @@ bool build_bvh(const Object &obj, const std::map<std::string, int> &matNames, in
 		box_add(bbox, tri_box(bvh.tris[n]));
 	Builder b{bvh, (flags & kUseSah) != 0};
 	b.push_node(bbox);
-	b.split(0, 0, (int)bvh.tris.size(), 0);
+	if(flags & kFastBuild)  // src/bvh/tree.cpp:311-314
+		b.split_binned(0, 0, (int)bvh.tris.size(), 0);
+	else
+		b.split(0, 0, (int)bvh.tris.size(), 0);
 	if(bvh.depth > Builder::maxDepth) {
 		err = "BVH deeper than maxDepth";
 		return false;

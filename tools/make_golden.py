@@ -78,6 +78,12 @@ def main():
         tri, t, bary = ref.trace_primary(cam, W, H)
         out["tri"], out["t"], out["bary"] = tri, t, bary
         out["dirs"] = ref.primary_dirs(cam, W, H)
+        # Reference quirk (src/scene_trace.cpp:410-411 simple shading, :316-330 full shading): a quad whose lane 0 missed never gets
+        # its Sample::normal initialised, and lanes of that quad that hit triangle 0 (== the "no object" value the
+        # missed lane was given, :374) are skipped by the per-lane fix-up (:423) -> they are shaded with whatever the
+        # stack held. Those pixels are undefined behaviour in the reference and are excluded from image goldens.
+        lane0 = np.repeat(tri[:, 0::4], 4, axis=1)[:, :W]
+        out["undef_simple"] = (tri == 0) & (lane0 < 0)
         rays = {}
         for stage, (gv, lit) in STAGES.items():
             ref.set_gvals(gv)
