@@ -183,6 +183,19 @@ int snl_render_dev(snl_scene *, const snl_camera *cam, int W, int H, const int *
 				   void *bgr8_dev, size_t pitch, int rank);
 int snl_scene_sync(snl_scene *, snl_stats *stats);
 
+/* Multi-GPU compose over NVLink peer memory (replaces the tile transport of src/node.cpp:20-120 / src/comm_mpi.cpp and
+ * the per-tile receive loop of src/server.cpp:330-418). Rank 0 creates the frame on its device and hands the 64-byte
+ * handle to the other ranks (any byte transport: torch.distributed broadcast in bench.py); each of them maps the SAME
+ * HBM buffer with snl_frame_open and passes the mapped pointer to snl_render_dev together with its own tile list:
+ * k_render then stores every pixel directly into rank 0's frame through NVSwitch - tracing and gather are one kernel,
+ * no staging copy and no collective on the data path. After every rank's snl_scene_sync (+ a host barrier) the frame is
+ * complete; snl_frame_read copies it to the host. pitch of a frame is W * 3. */
+#define SNL_IPC_HANDLE_BYTES 64
+int snl_frame_create(snl_scene *, int W, int H, void **bgr8_dev, unsigned char ipc_handle[SNL_IPC_HANDLE_BYTES]);
+int snl_frame_open(snl_scene *, const unsigned char ipc_handle[SNL_IPC_HANDLE_BYTES], void **bgr8_dev);
+int snl_frame_close(snl_scene *, void *bgr8_dev); /* frees (owner) or unmaps (peer) */
+int snl_frame_read(snl_scene *, const void *bgr8_dev, int W, int H, unsigned char *bgr8_host, size_t host_pitch);
+
 /* Number of kernels this library launched on the scene since creation (bench.py's gpu_launches). */
 uint64_t snl_scene_launch_count(snl_scene *);
 

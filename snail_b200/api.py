@@ -22,7 +22,7 @@ ABI_SYMBOLS = [
     "snl_trace_rays", "snl_trace_shadow", "snl_raytrace", "snl_render", "snl_render_dev", "snl_scene_sync",
     "snl_scene_launch_count", "snl_scene_stream", "snl_host_scene_load_obj", "snl_host_scene_free",
     "snl_host_scene_counts", "snl_host_scene_copy", "snl_host_scene_material", "snl_host_scene_texture",
-    "snl_scene_set_host_scene",
+    "snl_scene_set_host_scene", "snl_frame_create", "snl_frame_open", "snl_frame_close", "snl_frame_read",
 ]
 
 # reference record layouts (src/bvh/tree.h:60-72, src/triangle.h:133-135,181-230)
@@ -138,6 +138,10 @@ def load_library(counters: bool = False) -> C.CDLL:
     L.snl_host_scene_material.argtypes = [vp, i, C.POINTER(Material)]
     L.snl_host_scene_texture.argtypes = [vp, i, C.POINTER(Texture)]
     L.snl_scene_set_host_scene.argtypes = [vp, vp]
+    L.snl_frame_create.argtypes = [vp, i, i, C.POINTER(C.c_void_p), C.c_char_p]
+    L.snl_frame_open.argtypes = [vp, C.c_char_p, C.POINTER(C.c_void_p)]
+    L.snl_frame_close.argtypes = [vp, vp]
+    L.snl_frame_read.argtypes = [vp, vp, i, i, vp, C.c_size_t]
     _libs[path] = L
     return L
 
@@ -356,6 +360,28 @@ class Scene:
         st = Stats()
         self._check(self.L.snl_scene_sync(self.h, C.byref(st)))
         return st.as_dict()
+
+    # ---- frames shared between ranks (CUDA IPC over NVLink) ---------------------------------------------------
+    def frame_create(self, W, H):
+        """Returns (device pointer, 64-byte IPC handle) of a zeroed W x H BGR8 frame on this scene's device."""
+        p = C.c_void_p()
+        h = C.create_string_buffer(64)
+        self._check(self.L.snl_frame_create(self.h, W, H, C.byref(p), h))
+        return p.value, h.raw
+
+    def frame_open(self, handle: bytes):
+        p = C.c_void_p()
+        self._check(self.L.snl_frame_open(self.h, handle, C.byref(p)))
+        return p.value
+
+    def frame_close(self, ptr):
+        self._check(self.L.snl_frame_close(self.h, C.c_void_p(ptr)))
+
+    def frame_read(self, ptr, W, H, out=None):
+        if out is None:
+            out = np.zeros((H, W, 3), np.uint8)
+        self._check(self.L.snl_frame_read(self.h, C.c_void_p(ptr), W, H, _ptr(out), out.strides[0]))
+        return out
 
     def launch_count(self):
         return int(self.L.snl_scene_launch_count(self.h))

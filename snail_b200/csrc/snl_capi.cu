@@ -308,6 +308,10 @@ void snl_scene_destroy(snl_scene *s) {
 	for(auto &b : s->dScratch)
 		b.release();
 	s->dPackets.release();
+	for(void *p : s->peerFrames)
+		cudaIpcCloseMemHandle(p);
+	for(void *p : s->ownedFrames)
+		cudaFree(p);
 	if(s->ev0)
 		cudaEventDestroy(s->ev0);
 	if(s->ev1)
@@ -722,6 +726,71 @@ int snl_render(snl_scene *s, const snl_camera *cam, int W, int H, const int *til
 									   cudaMemcpyDeviceToHost, s->stream));
 		}
 	return sync_and_stats(s, stats);
+}
+
+// ---- frames shared between the ranks of one box (CUDA IPC over NVLink) ----------------------------------------------
+
+int snl_frame_create(snl_scene *s, int W, int H, void **bgr8_dev, unsigned char ipc_handle[SNL_IPC_HANDLE_BYTES]) {
+	SNL_REQUIRE(s && bgr8_dev && W > 0 && H > 0, SNL_ERR_INVALID, "bad argument");
+	static_assert(sizeof(cudaIpcMemHandle_t) == SNL_IPC_HANDLE_BYTES, "cudaIpcMemHandle_t is 64 bytes");
+	SNL_CUDA(cudaSetDevice(s->device));
+	void *p = nullptr;
+	SNL_CUDA(cudaMalloc(&p, (size_t)W * H * 3));
+	SNL_CUDA(cudaMemset(p, 0, (size_t)W * H * 3));
+	if(ipc_handle) {
+		cudaIpcMemHandle_t h;
+		cudaError_t e = cudaIpcGetMemHandle(&h, p);
+		if(e != cudaSuccess) {
+			cudaFree(p);
+			set_error("cudaIpcGetMemHandle failed: %s", cudaGetErrorString(e));
+			return SNL_ERR_CUDA;
+		}
+		memcpy(ipc_handle, &h, sizeof(h));
+	}
+	s->ownedFrames.push_back(p);
+	*bgr8_dev = p;
+	return SNL_OK;
+}
+
+int snl_frame_open(snl_scene *s, const unsigned char ipc_handle[SNL_IPC_HANDLE_BYTES], void **bgr8_dev) {
+	SNL_REQUIRE(s && ipc_handle && bgr8_dev, SNL_ERR_INVALID, "bad argument");
+	SNL_CUDA(cudaSetDevice(s->device));
+	cudaIpcMemHandle_t h;
+	memcpy(&h, ipc_handle, sizeof(h));
+	void *p = nullptr;
+	SNL_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+	s->peerFrames.push_back(p);
+	*bgr8_dev = p;
+	return SNL_OK;
+}
+
+int snl_frame_close(snl_scene *s, void *p) {
+	SNL_REQUIRE(s && p, SNL_ERR_INVALID, "bad argument");
+	SNL_CUDA(cudaSetDevice(s->device));
+	SNL_CUDA(cudaStreamSynchronize(s->stream));
+	for(size_t i = 0; i < s->ownedFrames.size(); i++)
+		if(s->ownedFrames[i] == p) {
+			s->ownedFrames.erase(s->ownedFrames.begin() + i);
+			SNL_CUDA(cudaFree(p));
+			return SNL_OK;
+		}
+	for(size_t i = 0; i < s->peerFrames.size(); i++)
+		if(s->peerFrames[i] == p) {
+			s->peerFrames.erase(s->peerFrames.begin() + i);
+			SNL_CUDA(cudaIpcCloseMemHandle(p));
+			return SNL_OK;
+		}
+	set_error("not a frame of this scene");
+	return SNL_ERR_INVALID;
+}
+
+int snl_frame_read(snl_scene *s, const void *bgr8_dev, int W, int H, unsigned char *bgr8_host, size_t host_pitch) {
+	SNL_REQUIRE(s && bgr8_dev && bgr8_host && W > 0 && H > 0 && host_pitch >= (size_t)W * 3, SNL_ERR_INVALID, "bad argument");
+	SNL_CUDA(cudaSetDevice(s->device));
+	SNL_CUDA(cudaMemcpy2DAsync(bgr8_host, host_pitch, bgr8_dev, (size_t)W * 3, (size_t)W * 3, H, cudaMemcpyDeviceToHost,
+							   s->stream));
+	SNL_CUDA(cudaStreamSynchronize(s->stream));
+	return SNL_OK;
 }
 
 static int set_host_scene(snl_scene *s, const HostScene &hs) {

@@ -87,4 +87,6 @@ struct snl_scene {
 	int nPackets = 0;
 
 	uint64_t launches = 0;
+
+	std::vector<void *> ownedFrames, peerFrames;  // snl_frame_create / snl_frame_open
 };

@@ -98,3 +98,59 @@ def reduce_stats(dist, stats: dict, device=None) -> dict:
     dist.all_reduce(t, op=dist.ReduceOp.SUM)
     out = {k: int(v) for k, v in zip(keys, t.tolist())}
     return out
+
+
+class Farm:
+    """Render() over the ranks of one box: the counterpart of the reference's server loop (src/server.cpp:266-420)
+    with `dist` = an initialised torch.distributed (NCCL) process group and `scene` = this rank's snail_b200.Scene
+    holding a replica of the scene. compose = "p2p" (default; peer stores into rank 0's frame) or "gather"."""
+
+    def __init__(self, scene, dist, W: int, H: int, compose: str = "p2p", seed: int = 1):
+        self.scene, self.dist, self.W, self.H, self.compose = scene, dist, W, H, compose
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        self.tiles = tiles_for_rank(W, H, self.rank, self.world, seed) if self.world > 1 else None
+        self.seed = seed
+        self.image = None
+        if compose == "p2p":
+            handle = [None]
+            if self.rank == 0:
+                self.frame, handle[0] = scene.frame_create(W, H)
+            dist.broadcast_object_list(handle, src=0)
+            if self.rank != 0:
+                self.frame = scene.frame_open(handle[0])
+        else:
+            import torch
+            self.image = torch.zeros((H, W, 3), dtype=torch.uint8, device=torch.device("cuda", scene.device))
+            self.frame = self.image.data_ptr()
+
+    def render_async(self, cam):
+        """Launches this rank's tiles (asynchronous on the scene's stream)."""
+        self.scene.render_dev(cam, self.W, self.H, self.frame, self.W * 3, tiles=self.tiles, rank=self.rank)
+
+    def finish(self):
+        """Waits for this rank's kernels, completes the compose; returns this rank's stats."""
+        st = self.scene.sync()
+        if self.image is not None:
+            gather_frame(self.dist, self.image, self.W, self.H, self.rank, self.world, self.seed)
+        self.dist.barrier()  # p2p: every rank's stores have landed in rank 0's frame
+        return st
+
+    def render(self, cam, out=None):
+        """Whole frame: returns (image on rank 0 else None, TreeStats summed over the ranks)."""
+        import torch
+        self.render_async(cam)
+        st = self.finish()
+        total = reduce_stats(self.dist, st, device=torch.device("cuda", self.scene.device))
+        img = None
+        if self.rank == 0:
+            img = self.scene.frame_read(self.frame, self.W, self.H, out=out)
+        return img, total
+
+    def close(self):
+        self.dist.barrier()
+        if self.compose == "p2p":
+            if self.rank != 0:
+                self.scene.frame_close(self.frame)
+            self.dist.barrier()
+            if self.rank == 0:
+                self.scene.frame_close(self.frame)
