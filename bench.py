@@ -26,7 +26,7 @@ import numpy as np  # noqa: E402
 
 METRIC = "Mrays/s on sponza 1080p Whitted (1/2/4/8 B200) vs host-CPU tracer"
 UNIT = "Mrays/s"
-DEFAULT_WORKLOAD = "barracks_whitted"
+DEFAULT_WORKLOAD = "sponza_like_whitted"
 
 
 def parse_args():

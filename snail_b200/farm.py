@@ -71,22 +71,39 @@ def unpack_tiles(buf, tiles: np.ndarray, img) -> None:
         off += n
 
 
+_INDEX_CACHE = {}
+
+
+def tile_byte_index(tiles: np.ndarray, W: int) -> np.ndarray:
+    """Byte offsets (into a tightly packed H x W x 3 frame) of the pixels of `tiles`, in pack_tiles order."""
+    parts = []
+    for x, y, w, h in tiles.tolist():
+        rows = (np.arange(y, y + h, dtype=np.int64)[:, None] * W + np.arange(x, x + w, dtype=np.int64)[None, :]) * 3
+        parts.append((rows[:, :, None] + np.arange(3, dtype=np.int64)).reshape(-1))
+    return np.concatenate(parts) if parts else np.zeros(0, np.int64)
+
+
 def gather_frame(dist, img, W: int, H: int, rank: int, world: int, seed: int = 1):
     """"gather" compose: every rank contributes the tiles it rendered into its own copy of `img` (torch uint8
-    (H, W, 3), CPU for gloo / CUDA for NCCL); on return rank 0's `img` holds the whole frame."""
+    (H, W, 3), CPU for gloo / CUDA for NCCL); on return rank 0's `img` holds the whole frame. Packing and scattering
+    are one indexed copy each (index tensors cached per (W, H, world, device))."""
     import torch
     if world == 1:
         return img
-    all_tiles = [tiles_for_rank(W, H, r, world, seed) for r in range(world)]
-    size = max(tile_bytes(t) for t in all_tiles)
+    key = (W, H, world, seed, str(img.device))
+    if key not in _INDEX_CACHE:
+        idx = [torch.from_numpy(tile_byte_index(tiles_for_rank(W, H, r, world, seed), W)).to(img.device)
+               for r in range(world)]
+        _INDEX_CACHE[key] = (idx, max(int(i.numel()) for i in idx))
+    idx, size = _INDEX_CACHE[key]
+    flat = img.view(-1)
     mine = torch.zeros(size, dtype=torch.uint8, device=img.device)
-    packed = pack_tiles(img, all_tiles[rank])
-    mine[: packed.numel()] = packed
+    mine[: idx[rank].numel()] = flat[idx[rank]]
     bufs = [torch.empty_like(mine) for _ in range(world)] if rank == 0 else None
     dist.gather(mine, bufs, dst=0)
     if rank == 0:
         for r in range(1, world):
-            unpack_tiles(bufs[r], all_tiles[r], img)
+            flat[idx[r]] = bufs[r][: idx[r].numel()]
     return img
 
 

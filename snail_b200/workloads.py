@@ -10,6 +10,14 @@ DATA = os.path.join(ROOT, "data")
 
 # name -> (obj, mtl (authored, in data/) or None, inside-camera?, gVals, lit?, description)
 WORKLOADS = {
+    # BASELINE.json metric config ("sponza 1080p Whitted"): scenes/sponza.obj and its textures are absent from the
+    # reference checkout, so the default workload is a procedurally generated atrium of the same shape (268 K
+    # triangles, 12 textured + 1 Uber + 1 default material, interior camera) - tools/make_sponza_like.py.
+    "sponza_like_whitted": dict(obj="sponza_like.obj", mtl="@sponza_like.mtl", inside=True, gvals={6: 1, 7: 1}, lit=True,
+                                desc="sponza_like.obj (procedural stand-in for the absent sponza.obj: 267 936 tris, textured, "
+                                     "camera inside), Whitted: primary + shadow + 1 reflection, 1 point light"),
+    "sponza_like_shadow": dict(obj="sponza_like.obj", mtl="@sponza_like.mtl", inside=True, gvals={6: 1}, lit=True,
+                               desc="sponza_like.obj textured, primary + shadow"),
     # BASELINE.json configs[1] / metric: sponza.obj is absent from the reference checkout (.MISSING_LARGE_BLOBS);
     # SURVEY.md §8(d) names barracks.obj + data/347.png as the textured substitute.
     "barracks_whitted": dict(obj="barracks.obj", mtl="barracks.mtl", inside=False, gvals={6: 1, 7: 1}, lit=True,
@@ -41,6 +49,10 @@ def resolve(name: str) -> dict:
     w = dict(WORKLOADS[name])
     w["name"] = name
     w["obj_path"] = find_asset("scenes", w["obj"])
-    w["mtl_path"] = os.path.join(DATA, w["mtl"]) if w["mtl"] else None
-    w["tex_dir"] = os.path.dirname(find_asset("data", "347.png")) + "/" if w["mtl"] else ""
+    if w["mtl"] and w["mtl"].startswith("@"):  # generated next to its textures, under assets/data
+        w["mtl_path"] = find_asset("data", w["mtl"][1:])
+        w["tex_dir"] = os.path.dirname(w["mtl_path"]) + "/"
+    else:
+        w["mtl_path"] = os.path.join(DATA, w["mtl"]) if w["mtl"] else None
+        w["tex_dir"] = os.path.dirname(find_asset("data", "347.png")) + "/" if w["mtl"] else ""
     return w

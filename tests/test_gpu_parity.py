@@ -281,3 +281,35 @@ def test_unsupported_options_fail_loudly(sb):
         sc.set_options({9: 1})
     with pytest.raises(sb.SnlError):
         sc.trace_primary(sb.Camera((0, 0, 0)), 16, 16)  # no geometry yet
+
+
+def test_render_sponza_like_vs_oracle(sb):
+    """The bench workload (procedural sponza stand-in, tools/make_sponza_like.py): 268 K triangles, 11 textures,
+    Tex + Uber + default materials, interior camera; host ingest on OUR side, the reference's loader on the other."""
+    from snail_b200 import workloads
+    try:
+        w = workloads.resolve("sponza_like_whitted")
+    except FileNotFoundError as e:
+        pytest.skip(str(e))
+    R = need_oracle("scalar")
+    ref = R.RefScene(w["obj_path"], w["mtl_path"], w["tex_dir"], variant="scalar")
+    sc = sb.Scene(0)
+    sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"])
+    cam, light = sb.bench_camera(*ref.bbox(), inside=True)
+    W, H = 1920, 1080
+    tri_r, t_r, b_r = ref.trace_primary(cam.as_array(), W, H)
+    tri_g, t_g, b_g = sc.trace_primary(cam, W, H)
+    unexplained, ndiff, max_rel = classify_hits(tri_g, t_g, b_g, tri_r, t_r, b_r, T_REL_SCALAR)
+    print(f"sponza_like: id mismatches {ndiff}/{W*H}, unexplained {unexplained}, max rel t err {max_rel:.3g}")
+    assert unexplained == 0 and ndiff <= 1e-4 * W * H and max_rel <= T_REL_SCALAR
+    for gv in ({6: 1}, {6: 1, 7: 1}):
+        ref.set_gvals(gv)
+        ref.set_lights([[*light.pos, *light.color, light.radius]])
+        img_r, st_r, _ = ref.render(cam.as_array(), W, H, threads=16)
+        sc.set_options(gv)
+        sc.set_lights([light])
+        img_g, st_g = sc.render(cam, W, H)
+        ok1, exact, mx = image_stats(img_g, img_r)
+        print(f"sponza_like {gv}: <=1: {ok1*100:.4f}% identical {exact*100:.4f}% max {mx} rays gpu {st_g['rays']} ref {st_r['rays']}")
+        assert ok1 >= 0.999
+        assert abs(st_g["rays"] - st_r["rays"]) <= 0.002 * st_r["rays"]
