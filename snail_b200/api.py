@@ -98,7 +98,7 @@ _libs: dict[str, C.CDLL] = {}
 
 
 def load_library(counters: bool = False) -> C.CDLL:
-    path = LIB_COUNTERS_PATH if counters else LIB_PATH
+    path = LIB_COUNTERS_PATH if counters else os.environ.get("SNL_LIB", LIB_PATH)  # SNL_LIB: tuning variants
     if path in _libs:
         return _libs[path]
     if not os.path.exists(path):

@@ -39,13 +39,17 @@ def _stale(target: str) -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_library(force: bool = False, counters: bool = False, verbose: bool = False) -> str:
+def build_library(force: bool = False, counters: bool = False, verbose: bool = False, extra=(), suffix: str = "") -> str:
+    """extra / suffix: experimental variants (extra nvcc flags -> libsnail_b200<suffix>.so, picked up through SNL_LIB)."""
     target = LIB_COUNTERS if counters else LIB
+    if suffix:
+        target = target[:-3] + suffix + ".so"
     if not force and not _stale(target):
         return target
     flags = [f for f in NVCC_FLAGS if f != "--use_fast_math=false"]
     if counters:
         flags += ["-DSNL_COUNTERS"]
+    flags += list(extra)
     if verbose:
         flags += ["-Xptxas", "-v"]
     cmd = [_nvcc(), "-shared", *flags, "-I", os.path.join(HERE, "..", "include"),
@@ -60,5 +64,8 @@ def build_library(force: bool = False, counters: bool = False, verbose: bool = F
 
 
 if __name__ == "__main__":
-    path = build_library(force="--force" in sys.argv, counters="--counters" in sys.argv, verbose="-v" in sys.argv)
+    extra = [a for a in sys.argv[1:] if a.startswith("-D") or a.startswith("-maxrregcount")]
+    suffix = next((a.split("=", 1)[1] for a in sys.argv[1:] if a.startswith("--suffix=")), "")
+    path = build_library(force="--force" in sys.argv, counters="--counters" in sys.argv, verbose="-v" in sys.argv,
+                         extra=extra, suffix=suffix)
     print(path)

@@ -184,7 +184,9 @@ int ensure_pre(snl_scene *s, PreCacheEntry &e, const float origin[3]) {
 	if(e.valid && memcmp(e.origin, origin, 12) == 0)
 		return SNL_OK;
 	SNL_CUDA(e.buf.reserve((size_t)s->nTris));
-	SNL_CUDA(launch_pretransform(s->dTris.ptr, s->nTris, origin, e.buf.ptr, s->stream));
+	SNL_CUDA(e.nodes.reserve((size_t)s->nGpuNodes));
+	SNL_CUDA(launch_pretransform(s->dTris.ptr, s->nTris, s->dNodes.ptr, s->nGpuNodes, origin, e.buf.ptr, e.nodes.ptr,
+								 s->stream));
 	s->launches++;
 	memcpy(e.origin, origin, 12);
 	e.valid = true;
@@ -207,7 +209,7 @@ int make_scene_dev(snl_scene *s, SceneDev &S) {
 		int r = ensure_pre(s, s->lightPre[i], l.pos);
 		if(r)
 			return r;
-		S.lightPre[i] = s->lightPre[i].buf.ptr;
+		S.lightPre[i] = s->lightPre[i].set();
 		memcpy(S.lights[i].pos, l.pos, 12);
 		memcpy(S.lights[i].color, l.color, 12);
 		S.lights[i].radius = l.radius;
@@ -219,6 +221,7 @@ int make_scene_dev(snl_scene *s, SceneDev &S) {
 	S.gvFull = s->gVals[6];
 	S.gvRefl = s->gVals[7];
 	S.gvTint = 0;
+	S.hasUber = s->hasUber;
 	S.counters = s->dCounters.ptr;
 	return SNL_OK;
 }
@@ -300,9 +303,12 @@ void snl_scene_destroy(snl_scene *s) {
 	s->dTexs.release();
 	for(auto &t : s->dTexData)
 		t.release();
-	for(auto &e : s->lightPre)
+	for(auto &e : s->lightPre) {
 		e.buf.release();
+		e.nodes.release();
+	}
 	s->originPre.buf.release();
+	s->originPre.nodes.release();
 	s->dCounters.release();
 	s->dImage.release();
 	for(auto &b : s->dScratch)
@@ -444,6 +450,9 @@ static int upload_materials(snl_scene *s, const snl_material *mats, int nMats, c
 	if(nMats)
 		SNL_CUDA(cudaMemcpy(s->dMats.ptr, dm.data(), nMats * sizeof(DevMaterial), cudaMemcpyHostToDevice));
 	s->nMats = nMats;
+	s->hasUber = 0;
+	for(int i = 0; i < nMats; i++)
+		s->hasUber |= mats[i].kind == SNL_MAT_UBER;
 	return SNL_OK;
 }
 
@@ -540,7 +549,7 @@ int snl_trace_primary(snl_scene *s, const snl_camera *cam, int W, int H, int *tr
 	SNL_TRY(ensure_pre(s, s->originPre, cam->pos));
 	RayGenParams g;
 	make_raygen(*cam, W, H, g);
-	SNL_CUDA(launch_primary(S, s->originPre.buf.ptr, g, W, H, dId, dT, dB, s->stream));
+	SNL_CUDA(launch_primary(S, s->originPre.set(), g, W, H, dId, dT, dB, s->stream));
 	s->launches++;
 	SNL_TRY(end_call(s));
 	if(triId)
@@ -586,7 +595,7 @@ int snl_trace_rays(snl_scene *s, const float *o3, const float *d3, const unsigne
 	SNL_TRY(make_scene_dev(s, S));
 	if(sharedOrigin)
 		SNL_TRY(ensure_pre(s, s->originPre, o3));
-	SNL_CUDA(launch_trace_rays(S, s->originPre.buf.ptr, dO, dD, dM, n, sharedOrigin != 0, dId, dT, dB, s->stream));
+	SNL_CUDA(launch_trace_rays(S, s->originPre.set(), dO, dD, dM, n, sharedOrigin != 0, dId, dT, dB, s->stream));
 	s->launches++;
 	SNL_TRY(end_call(s));
 	if(triId)
@@ -611,7 +620,7 @@ int snl_trace_shadow(snl_scene *s, const float origin[3], const float *d3, float
 	SceneDev S;
 	SNL_TRY(make_scene_dev(s, S));
 	SNL_TRY(ensure_pre(s, s->originPre, origin));
-	SNL_CUDA(launch_trace_shadow(S, s->originPre.buf.ptr, origin, dD, dT, n, s->stream));
+	SNL_CUDA(launch_trace_shadow(S, s->originPre.set(), origin, dD, dT, n, s->stream));
 	s->launches++;
 	SNL_TRY(end_call(s));
 	SNL_CUDA(cudaMemcpyAsync(tmax_inout, dT, (size_t)n * 4, cudaMemcpyDeviceToHost, s->stream));
@@ -632,7 +641,7 @@ int snl_raytrace(snl_scene *s, const float *o3, const float *d3, const unsigned 
 	SNL_TRY(make_scene_dev(s, S));
 	if(sharedOrigin)
 		SNL_TRY(ensure_pre(s, s->originPre, o3));
-	SNL_CUDA(launch_raytrace(S, s->originPre.buf.ptr, dO, dD, dM, n, sharedOrigin != 0, dC, s->stream));
+	SNL_CUDA(launch_raytrace(S, s->originPre.set(), dO, dD, dM, n, sharedOrigin != 0, dC, s->stream));
 	s->launches++;
 	SNL_TRY(end_call(s));
 	SNL_CUDA(cudaMemcpyAsync(rgb3, dC, (size_t)n * 12, cudaMemcpyDeviceToHost, s->stream));
@@ -687,7 +696,7 @@ static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, cons
 		SNL_TRY(ensure_packets(s, tiles, nTiles, W, H));
 		packets = s->dPackets.ptr;
 	}
-	SNL_CUDA(launch_render(S, s->originPre.buf.ptr, g, W, H, packets, s->nPackets, dOut, pitch, s->stream));
+	SNL_CUDA(launch_render(S, s->originPre.set(), g, W, H, packets, s->nPackets, dOut, pitch, s->stream));
 	s->launches++;
 	return SNL_OK;
 }

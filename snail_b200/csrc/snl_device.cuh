@@ -45,6 +45,23 @@ __device__ __forceinline__ bool box_test(float minx, float maxx, float miny, flo
 	return lmax >= 0.0f && lmin <= fminf(lmax, dist);
 }
 
+// The same test on a box already translated by the ray origin (minx = box.min.x - origin.x, ...).
+__device__ __forceinline__ bool box_test_rel(float minx, float maxx, float miny, float maxy, float minz, float maxz, float ix,
+											 float iy, float iz, float dist, float &lminOut) {
+	float l1 = ix * minx, l2 = ix * maxx;
+	float lmin = fminf(l1, l2), lmax = fmaxf(l1, l2);
+	l1 = iy * miny;
+	l2 = iy * maxy;
+	lmin = fmaxf(lmin, fminf(l1, l2));
+	lmax = fminf(lmax, fmaxf(l1, l2));
+	l1 = iz * minz;
+	l2 = iz * maxz;
+	lmin = fmaxf(lmin, fminf(l1, l2));
+	lmax = fminf(lmax, fmaxf(l1, l2));
+	lminOut = lmin;
+	return lmax >= 0.0f && lmin <= fminf(lmax, dist);
+}
+
 struct Hit {
 	float dist;
 	int obj;
@@ -100,96 +117,133 @@ __device__ __forceinline__ void tri_nearest_gen(const GenTri *__restrict__ t, in
 	}
 }
 
-// BVH::TraversePrimaryN per ray (src/bvh/traverse.cpp:14-80). Per-thread stack, children visited nearest first
-// (by slab entry distance instead of the packet's firstNode^sign[axis]; only exact-t ties can differ).
+// ---- traversal ------------------------------------------------------------------------------------------------------
+// Per-thread stack, "while-while" order (Aila & Laine): a lane walks inner nodes until it reaches a leaf, parks the
+// leaf and keeps walking until every lane of the warp has one parked (or has run out of nodes); then the warp tests
+// triangles together. Inner-node code and triangle code each run with most lanes active instead of interleaving.
+// Children are visited nearest first (by slab entry distance instead of the packet's firstNode^sign[axis]); only
+// exact-t ties can resolve differently from the reference's packet order.
+//
+// SHARED rays (one origin for the whole launch: camera or light) read node boxes that were translated by the origin
+// once per frame (k_pretransform: the very subtraction `min - origin` the reference performs per packet per node,
+// src/bounding_box.cpp:68-71, so the products are bit-identical) and PreTri records; per-ray-origin rays read the
+// untranslated nodes and GenTri records.
+
+enum { kSentinel = 0x7fffffff };
+
+// One step of the walk after the two box tests of the node at `cur`: go to the nearer hit child (push the farther), or
+// pop; a leaf reached while none is parked gets parked and the walk continues with the next stack entry. stack[-1]
+// reads (sp == 0 when tos is the sentinel) cannot happen: the sentinel ends the walk before it would be popped twice.
+#define SNL_TRAVERSE_STEP()                                   \
+	do {                                                      \
+		const bool both_ = h0 && h1, any_ = h0 || h1;         \
+		const bool swap_ = lmin1 < lmin0;                     \
+		int next_ = both_ ? (swap_ ? l1 : l0) : (h0 ? l0 : l1); \
+		if(both_) {                                           \
+			stack[sp++] = tos;                                \
+			tos = swap_ ? l0 : l1;                            \
+		}                                                     \
+		if(!any_) {                                           \
+			next_ = tos;                                      \
+			tos = stack[--sp];                                \
+		}                                                     \
+		if(next_ < 0 && leaf == 0) {                          \
+			leaf = next_;                                     \
+			next_ = tos;                                      \
+			tos = stack[--sp];                                \
+		}                                                     \
+		cur = next_;                                          \
+	} while(0)
+
+// Both children of one inner node. REL: boxes are already relative to the ray origin.
+template <bool REL>
+__device__ __forceinline__ void node_test(const GpuNode *__restrict__ n, float ox, float oy, float oz, float ix, float iy,
+										  float iz, float dist, bool &h0, bool &h1, float &lmin0, float &lmin1, int &l0, int &l1) {
+	const float4 b0 = ldg4(&n->b0), b1 = ldg4(&n->b1), bz = ldg4(&n->bz);
+	const int2 link = __ldg(reinterpret_cast<const int2 *>(&n->link));
+	l0 = link.x;
+	l1 = link.y;
+	if(REL) {
+		h0 = box_test_rel(b0.x, b0.y, b0.z, b0.w, bz.x, bz.y, ix, iy, iz, dist, lmin0);
+		h1 = box_test_rel(b1.x, b1.y, b1.z, b1.w, bz.z, bz.w, ix, iy, iz, dist, lmin1);
+	}
+	else {
+		h0 = box_test(b0.x, b0.y, b0.z, b0.w, bz.x, bz.y, ox, oy, oz, ix, iy, iz, dist, lmin0);
+		h1 = box_test(b1.x, b1.y, b1.z, b1.w, bz.z, bz.w, ox, oy, oz, ix, iy, iz, dist, lmin1);
+	}
+}
+
+// BVH::TraversePrimaryN per ray (src/bvh/traverse.cpp:14-80).
 template <bool SHARED>
 __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nodes, const void *__restrict__ tris,
 												 float ox, float oy, float oz, float dx, float dy, float dz, float ix,
 												 float iy, float iz, Hit &h, TravCount &tc) {
-	int stack[kStack];
+	// the top of the stack lives in a register (tos): a pop hands out the next node without waiting for local memory
+	int stackMem[kStack + 1];  // [0] is a guard slot: popping the sentinel reads stack[-1]
+	int *const stack = stackMem + 1;
 	int sp = 0;
+	int tos = kSentinel;
 	int cur = 0;
-	for(;;) {
-		if(cur >= 0) {
+	while(cur != kSentinel) {
+		int leaf = 0;  // parked leaf link (< 0), 0 = none
+		while((unsigned)cur < (unsigned)kSentinel) {
 			SNL_COUNT(tc.nodes);
-			const GpuNode *n = nodes + cur;
-			const float4 b0 = ldg4(&n->b0), b1 = ldg4(&n->b1), bz = ldg4(&n->bz);
-			const int4 link = ldg4(&n->link);
+			bool h0, h1;
 			float lmin0, lmin1;
-			const bool h0 = box_test(b0.x, b0.y, b0.z, b0.w, bz.x, bz.y, ox, oy, oz, ix, iy, iz, h.dist, lmin0);
-			const bool h1 = box_test(b1.x, b1.y, b1.z, b1.w, bz.z, bz.w, ox, oy, oz, ix, iy, iz, h.dist, lmin1);
-			if(h0 && h1) {
-				const bool swap = lmin1 < lmin0;
-				stack[sp++] = swap ? link.x : link.y;
-				cur = swap ? link.y : link.x;
-				continue;
-			}
-			if(h0) {
-				cur = link.x;
-				continue;
-			}
-			if(h1) {
-				cur = link.y;
-				continue;
-			}
+			int l0, l1;
+			node_test<SHARED>(nodes + cur, ox, oy, oz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
+			SNL_TRAVERSE_STEP();
+			if(!__any_sync(__activemask(), leaf == 0))
+				break;
 		}
-		else {
-			const int leaf = ~cur;
-			const int first = leaf & kLeafFirstMask, count = (leaf >> kLeafFirstBits) + 1;
+		while(leaf < 0) {
+			const int lf = ~leaf;
+			const int first = lf & kLeafFirstMask, count = (lf >> kLeafFirstBits) + 1;
 			for(int i = 0; i < count; i++) {
-				if(SHARED)
+				if(SHARED) {
 					SNL_COUNT(tc.tris);
-				else
-					SNL_COUNT(tc.gtris);
-				if(SHARED)
 					tri_nearest_pre(reinterpret_cast<const PreTri *>(tris) + first + i, first + i, dx, dy, dz, h);
-				else
-					tri_nearest_gen(reinterpret_cast<const GenTri *>(tris) + first + i, first + i, ox, oy, oz, dx, dy,
-									dz, h);
+				}
+				else {
+					SNL_COUNT(tc.gtris);
+					tri_nearest_gen(reinterpret_cast<const GenTri *>(tris) + first + i, first + i, ox, oy, oz, dx, dy, dz, h);
+				}
+			}
+			leaf = cur;
+			if(cur < 0) {
+				cur = tos;
+				tos = stack[--sp];
 			}
 		}
-		if(sp == 0)
-			break;
-		cur = stack[--sp];
 	}
 }
 
 // BVH::TraverseShadow per ray (src/bvh/traverse.cpp:82-149) with Triangle::Collide(ShadowContext&)
 // (src/triangle.cpp:65-102): any hit, ONE-SIDED (only triangles with dir.nrm >= u+v >= 0 occlude), no division.
-// Origin = light position, so triangles are PreTri records of that light.
-__device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ nodes, const PreTri *__restrict__ tris, float ox,
-												float oy, float oz, float dx, float dy, float dz, float ix, float iy,
-												float iz, float dist, TravCount &tc) {
-	int stack[kStack];
+// Origin = light position: nodes are that light's translated boxes, triangles its PreTri records.
+__device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ nodes, const PreTri *__restrict__ tris, float dx,
+												float dy, float dz, float ix, float iy, float iz, float dist, TravCount &tc) {
+	int stackMem[kStack + 1];  // [0] is a guard slot: popping the sentinel reads stack[-1]
+	int *const stack = stackMem + 1;
 	int sp = 0;
+	int tos = kSentinel;
 	int cur = 0;
-	for(;;) {
-		if(cur >= 0) {
+	bool occluded = false;
+	while(cur != kSentinel) {
+		int leaf = 0;
+		while((unsigned)cur < (unsigned)kSentinel) {
 			SNL_COUNT(tc.nodes);
-			const GpuNode *n = nodes + cur;
-			const float4 b0 = ldg4(&n->b0), b1 = ldg4(&n->b1), bz = ldg4(&n->bz);
-			const int4 link = ldg4(&n->link);
+			bool h0, h1;
 			float lmin0, lmin1;
-			const bool h0 = box_test(b0.x, b0.y, b0.z, b0.w, bz.x, bz.y, ox, oy, oz, ix, iy, iz, dist, lmin0);
-			const bool h1 = box_test(b1.x, b1.y, b1.z, b1.w, bz.z, bz.w, ox, oy, oz, ix, iy, iz, dist, lmin1);
-			if(h0 && h1) {
-				const bool swap = lmin1 < lmin0;
-				stack[sp++] = swap ? link.x : link.y;
-				cur = swap ? link.y : link.x;
-				continue;
-			}
-			if(h0) {
-				cur = link.x;
-				continue;
-			}
-			if(h1) {
-				cur = link.y;
-				continue;
-			}
+			int l0, l1;
+			node_test<true>(nodes + cur, 0.0f, 0.0f, 0.0f, ix, iy, iz, dist, h0, h1, lmin0, lmin1, l0, l1);
+			SNL_TRAVERSE_STEP();
+			if(!__any_sync(__activemask(), leaf == 0))
+				break;
 		}
-		else {
-			const int leaf = ~cur;
-			const int first = leaf & kLeafFirstMask, count = (leaf >> kLeafFirstBits) + 1;
+		while(leaf < 0) {
+			const int lf = ~leaf;
+			const int first = lf & kLeafFirstMask, count = (lf >> kLeafFirstBits) + 1;
 			for(int i = 0; i < count; i++) {
 				SNL_COUNT(tc.tris);
 				const PreTri *t = tris + first + i;
@@ -199,14 +253,20 @@ __device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ node
 				const float u = dx * tu.x + dy * tu.y + dz * tu.z;
 				const float tmul = tu.w;
 				if(fminf(u, v) >= 0.0f && u + v <= det && tmul > 0.0f && tmul < dist * det)
-					return true;
+					occluded = true;
+			}
+			if(occluded) {
+				cur = kSentinel;
+				break;
+			}
+			leaf = cur;
+			if(cur < 0) {
+				cur = tos;
+				tos = stack[--sp];
 			}
 		}
-		if(sp == 0)
-			break;
-		cur = stack[--sp];
 	}
-	return false;
+	return occluded;
 }
 
 // SafeInv (src/rtbase.h:117-119): Inv(v + 1e-8).
@@ -439,8 +499,8 @@ __device__ __forceinline__ bool trace_light(const SceneDev &S, int li, bool sel,
 	if(!(dot > 0.0f))
 		return false;
 	const float tmax = distance * 0.9999f;
-	const bool occluded = traverse_shadow(S.nodes, S.lightPre[li], L.pos[0], L.pos[1], L.pos[2], fx, fy, fz, safe_inv(fx),
-										  safe_inv(fy), safe_inv(fz), tmax, tc);
+	const bool occluded = traverse_shadow(S.lightPre[li].nodes, S.lightPre[li].tris, fx, fy, fz, safe_inv(fx), safe_inv(fy),
+										  safe_inv(fz), tmax, tc);
 	if(!occluded && tmax > 0.0f) {
 		float atten = distance * L.iRadius;
 		const float x = ((1.0f - atten) * 0.2f + 1.0f / (16.0f * atten * atten)) - 0.0625f;
@@ -469,7 +529,7 @@ struct PacketCounts {
 // Scene::RayTrace for the calling lane (src/scene_trace.cpp:92-520). LEVEL 0 = the caller's rays, LEVEL 1 = the
 // reflection pass (cache.reflections == 1: no further bounce). All 256 threads of the CTA must call it.
 template <int LEVEL, bool SHARED>
-__device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreTri *__restrict__ originPre, bool active,
+__device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet originPre, bool active,
 											  bool packetHasMask, float ox, float oy, float oz, float dx, float dy,
 											  float dz, float &outr, float &outg, float &outb, PacketCounts &pc,
 											  TravCount &tc) {
@@ -480,7 +540,7 @@ __device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreTri *_
 	if(active) {
 		const float ix = safe_inv(dx), iy = safe_inv(dy), iz = safe_inv(dz);
 		if(SHARED)
-			traverse_nearest<true>(S.nodes, originPre, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
+			traverse_nearest<true>(originPre.nodes, originPre.tris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
 		else
 			traverse_nearest<false>(S.nodes, S.gtris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
 		if(LEVEL == 0)
@@ -503,13 +563,15 @@ __device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreTri *_
 	shade_block(S, sel, h, ox, oy, oz, dx, dy, dz, packetHasMask, s);
 
 	if(LEVEL == 0 && S.gvRefl) {  // src/scene_trace.cpp:454-466, TraceReflection :603-618
-		const bool all = __syncthreads_and(sel);
+		// selector.All() of the packet (src/scene_trace.cpp:615-617) picks RayGroup<0,0> or <0,1> for the bounce; only
+		// UberMaterial::Shade_ looks at it, so the CTA-wide vote is skipped for scenes without one
+		const bool all = S.hasUber ? (bool)__syncthreads_and(sel) : true;
 		const float dot = s.nx * dx + s.ny * dy + s.nz * dz;
 		const float dd = dot + dot;
 		const float rx = dx - s.nx * dd, ry = dy - s.ny * dd, rz = dz - s.nz * dd;
 		const float rox = s.px + rx * 0.001f, roy = s.py + ry * 0.001f, roz = s.pz + rz * 0.001f;
 		float cr = 0.0f, cg = 0.0f, cb = 0.0f;
-		raytrace_lane<1, false>(S, nullptr, sel, !all, rox, roy, roz, rx, ry, rz, cr, cg, cb, pc, tc);
+		raytrace_lane<1, false>(S, PreSet{nullptr, nullptr}, sel, !all, rox, roy, roz, rx, ry, rz, cr, cg, cb, pc, tc);
 		if(sel) {
 			s.dr = s.dr + (cr - s.dr) * 0.3f;
 			s.dg = s.dg + (cg - s.dg) * 0.3f;

@@ -4,10 +4,22 @@
 
 namespace snl {
 
-// Triangle::Collide sharedOrigin precomputation (src/triangle.cpp:9-18) for every triangle and one origin.
-__global__ void __launch_bounds__(256) k_pretransform(const GenTri *__restrict__ gtris, int nTris, float ox, float oy,
-													 float oz, PreTri *__restrict__ out) {
+// Per-origin records, one launch per origin and frame: Triangle::Collide's sharedOrigin precomputation
+// (src/triangle.cpp:9-18) for every triangle, and every node's child boxes translated by the origin (the
+// `min - origin` / `max - origin` of BBox::Test, src/bounding_box.cpp:68-71, hoisted out of the traversal loop).
+__global__ void __launch_bounds__(256) k_pretransform(const GenTri *__restrict__ gtris, int nTris,
+													 const GpuNode *__restrict__ nodes, int nNodes, float ox, float oy,
+													 float oz, PreTri *__restrict__ out, GpuNode *__restrict__ outNodes) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
+	if(i < nNodes) {
+		const float4 b0 = ldg4(&nodes[i].b0), b1 = ldg4(&nodes[i].b1), bz = ldg4(&nodes[i].bz);
+		const int4 link = ldg4(&nodes[i].link);
+		float4 *o = reinterpret_cast<float4 *>(outNodes + i);
+		o[0] = make_float4(b0.x - ox, b0.y - ox, b0.z - oy, b0.w - oy);
+		o[1] = make_float4(b1.x - ox, b1.y - ox, b1.z - oy, b1.w - oy);
+		o[2] = make_float4(bz.x - oz, bz.y - oz, bz.z - oz, bz.w - oz);
+		reinterpret_cast<int4 *>(outNodes + i)[3] = link;
+	}
 	if(i >= nTris)
 		return;
 	const float4 ta = ldg4(&gtris[i].a), tba = ldg4(&gtris[i].ba), tca = ldg4(&gtris[i].ca), tn = ldg4(&gtris[i].n);
@@ -33,7 +45,7 @@ __global__ void __launch_bounds__(256) k_pretransform(const GenTri *__restrict__
 
 // ---- BVH::TraversePrimary on generated primary rays (snl_trace_primary) -------------------------------------
 // grid = packets (16x16 pixels), block = 256.
-__global__ void __launch_bounds__(kPacket) k_primary(SceneDev S, const PreTri *__restrict__ pre, RayGenParams g, int W, int H,
+__global__ void __launch_bounds__(kPacket) k_primary(SceneDev S, const PreSet pre, RayGenParams g, int W, int H,
 												  int packetsX, int *__restrict__ triId, float *__restrict__ t,
 												  float *__restrict__ bary) {
 	const int px0 = (blockIdx.x % packetsX) * 16, py0 = (blockIdx.x / packetsX) * 16;
@@ -49,7 +61,7 @@ __global__ void __launch_bounds__(kPacket) k_primary(SceneDev S, const PreTri *_
 		h.dist = CUDART_INF_F;
 		h.obj = 0;
 		h.bu = h.bv = 0.0f;
-		traverse_nearest<true>(S.nodes, pre, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, safe_inv(dx), safe_inv(dy),
+		traverse_nearest<true>(pre.nodes, pre.tris, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, safe_inv(dx), safe_inv(dy),
 							   safe_inv(dz), h, tc);
 		pc.primary = 1;
 		const size_t o = (size_t)y * W + x;
@@ -69,7 +81,7 @@ __global__ void __launch_bounds__(kPacket) k_primary(SceneDev S, const PreTri *_
 
 // ---- BVH::TraversePrimary on caller rays (snl_trace_rays) ---------------------------------------------------
 template <bool SHARED>
-__global__ void __launch_bounds__(kPacket) k_trace_rays(SceneDev S, const PreTri *__restrict__ pre, const float *__restrict__ o3,
+__global__ void __launch_bounds__(kPacket) k_trace_rays(SceneDev S, const PreSet pre, const float *__restrict__ o3,
 													 const float *__restrict__ d3, const unsigned char *__restrict__ mask,
 													 int n, int *__restrict__ triId, float *__restrict__ t,
 													 float *__restrict__ bary) {
@@ -86,7 +98,7 @@ __global__ void __launch_bounds__(kPacket) k_trace_rays(SceneDev S, const PreTri
 			const float *o = SHARED ? o3 : o3 + (size_t)i * 3;
 			const float ox = o[0], oy = o[1], oz = o[2];
 			const float dx = d3[(size_t)i * 3 + 0], dy = d3[(size_t)i * 3 + 1], dz = d3[(size_t)i * 3 + 2];
-			traverse_nearest<SHARED>(S.nodes, SHARED ? (const void *)pre : (const void *)S.gtris, ox, oy, oz, dx, dy, dz,
+			traverse_nearest<SHARED>(SHARED ? pre.nodes : S.nodes, SHARED ? (const void *)pre.tris : (const void *)S.gtris, ox, oy, oz, dx, dy, dz,
 									 safe_inv(dx), safe_inv(dy), safe_inv(dz), h, tc);
 			pc.primary = 1;
 		}
@@ -105,7 +117,7 @@ __global__ void __launch_bounds__(kPacket) k_trace_rays(SceneDev S, const PreTri
 }
 
 // ---- BVH::TraverseShadow on caller rays from one origin (snl_trace_shadow) ----------------------------------
-__global__ void __launch_bounds__(kPacket) k_trace_shadow(SceneDev S, const PreTri *__restrict__ pre, float ox, float oy, float oz,
+__global__ void __launch_bounds__(kPacket) k_trace_shadow(SceneDev S, const PreSet pre, float ox, float oy, float oz,
 													   const float *__restrict__ d3, float *__restrict__ tmax, int n) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
 	PacketCounts pc = {0, 0, 0, 0};
@@ -114,7 +126,7 @@ __global__ void __launch_bounds__(kPacket) k_trace_shadow(SceneDev S, const PreT
 		const float dist = tmax[i];
 		if(dist >= 0.0f) {
 			const float dx = d3[(size_t)i * 3 + 0], dy = d3[(size_t)i * 3 + 1], dz = d3[(size_t)i * 3 + 2];
-			if(traverse_shadow(S.nodes, pre, ox, oy, oz, dx, dy, dz, safe_inv(dx), safe_inv(dy), safe_inv(dz), dist, tc))
+			if(traverse_shadow(pre.nodes, pre.tris, dx, dy, dz, safe_inv(dx), safe_inv(dy), safe_inv(dz), dist, tc))
 				tmax[i] = -CUDART_INF_F;
 			pc.shadow = 1;
 		}
@@ -125,7 +137,7 @@ __global__ void __launch_bounds__(kPacket) k_trace_shadow(SceneDev S, const PreT
 
 // ---- Scene::RayTrace on caller rays, 256-ray packets (snl_raytrace) -----------------------------------------
 template <bool SHARED>
-__global__ void __launch_bounds__(kPacket) k_raytrace(SceneDev S, const PreTri *__restrict__ pre, const float *__restrict__ o3,
+__global__ void __launch_bounds__(kPacket) k_raytrace(SceneDev S, const PreSet pre, const float *__restrict__ o3,
 												   const float *__restrict__ d3, const unsigned char *__restrict__ mask,
 												   int n, float *__restrict__ rgb3) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -160,7 +172,10 @@ __device__ __forceinline__ unsigned conv_channel(float c) {
 
 // ---- Render(): RenderTask::Work per packet (src/render.cpp:47-211) ------------------------------------------
 // grid = packets; packet p covers pixels [x0, x0+16) x [y0, y0+16) clipped to (cw, ch). `packets` == null: full image.
-__global__ void __launch_bounds__(kPacket) k_render(SceneDev S, const PreTri *__restrict__ pre, RayGenParams g, int W, int H,
+#ifndef SNL_RENDER_MIN_BLOCKS
+#define SNL_RENDER_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(kPacket, SNL_RENDER_MIN_BLOCKS) k_render(SceneDev S, const PreSet pre, RayGenParams g, int W, int H,
 												 int packetsX, const int4 *__restrict__ packets,
 												 unsigned char *__restrict__ out, size_t pitch) {
 	int px0, py0, cw, ch;
@@ -207,21 +222,23 @@ __global__ void __launch_bounds__(kPacket) k_render(SceneDev S, const PreTri *__
 
 static inline unsigned blocks_for(int n, int per) { return (unsigned)((n + per - 1) / per); }
 
-cudaError_t launch_pretransform(const GenTri *gtris, int nTris, const float origin[3], PreTri *out, cudaStream_t st) {
+cudaError_t launch_pretransform(const GenTri *gtris, int nTris, const GpuNode *nodes, int nNodes, const float origin[3],
+								PreTri *out, GpuNode *outNodes, cudaStream_t st) {
 	if(nTris <= 0)
 		return cudaSuccess;
-	k_pretransform<<<blocks_for(nTris, 256), 256, 0, st>>>(gtris, nTris, origin[0], origin[1], origin[2], out);
+	k_pretransform<<<blocks_for(nTris > nNodes ? nTris : nNodes, 256), 256, 0, st>>>(gtris, nTris, nodes, nNodes, origin[0],
+																					 origin[1], origin[2], out, outNodes);
 	return cudaGetLastError();
 }
 
-cudaError_t launch_primary(const SceneDev &S, const PreTri *pre, const RayGenParams &g, int W, int H, int *triId, float *t,
+cudaError_t launch_primary(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, int *triId, float *t,
 						   float *bary, cudaStream_t st) {
 	const int px = (W + 15) / 16, py = (H + 15) / 16;
 	k_primary<<<px * py, kPacket, 0, st>>>(S, pre, g, W, H, px, triId, t, bary);
 	return cudaGetLastError();
 }
 
-cudaError_t launch_trace_rays(const SceneDev &S, const PreTri *pre, const float *o3, const float *d3,
+cudaError_t launch_trace_rays(const SceneDev &S, const PreSet &pre, const float *o3, const float *d3,
 							  const unsigned char *mask, int n, bool shared, int *triId, float *t, float *bary,
 							  cudaStream_t st) {
 	if(n <= 0)
@@ -233,7 +250,7 @@ cudaError_t launch_trace_rays(const SceneDev &S, const PreTri *pre, const float 
 	return cudaGetLastError();
 }
 
-cudaError_t launch_trace_shadow(const SceneDev &S, const PreTri *pre, const float origin[3], const float *d3, float *tmax,
+cudaError_t launch_trace_shadow(const SceneDev &S, const PreSet &pre, const float origin[3], const float *d3, float *tmax,
 								int n, cudaStream_t st) {
 	if(n <= 0)
 		return cudaSuccess;
@@ -241,7 +258,7 @@ cudaError_t launch_trace_shadow(const SceneDev &S, const PreTri *pre, const floa
 	return cudaGetLastError();
 }
 
-cudaError_t launch_raytrace(const SceneDev &S, const PreTri *pre, const float *o3, const float *d3,
+cudaError_t launch_raytrace(const SceneDev &S, const PreSet &pre, const float *o3, const float *d3,
 							const unsigned char *mask, int n, bool shared, float *rgb3, cudaStream_t st) {
 	if(n <= 0)
 		return cudaSuccess;
@@ -252,7 +269,7 @@ cudaError_t launch_raytrace(const SceneDev &S, const PreTri *pre, const float *o
 	return cudaGetLastError();
 }
 
-cudaError_t launch_render(const SceneDev &S, const PreTri *pre, const RayGenParams &g, int W, int H, const int4 *packets,
+cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, const int4 *packets,
 						  int nPackets, unsigned char *out, size_t pitch, cudaStream_t st) {
 	const int px = (W + 15) / 16, py = (H + 15) / 16;
 	const int grid = packets ? nPackets : px * py;

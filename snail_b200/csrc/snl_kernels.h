@@ -8,18 +8,20 @@
 namespace snl {
 
 struct SceneDev;
+struct PreSet;
 
-cudaError_t launch_pretransform(const GenTri *gtris, int nTris, const float origin[3], PreTri *out, cudaStream_t st);
-cudaError_t launch_primary(const SceneDev &S, const PreTri *pre, const RayGenParams &g, int W, int H, int *triId, float *t,
+cudaError_t launch_pretransform(const GenTri *gtris, int nTris, const GpuNode *nodes, int nNodes, const float origin[3],
+								PreTri *out, GpuNode *outNodes, cudaStream_t st);
+cudaError_t launch_primary(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, int *triId, float *t,
 						   float *bary, cudaStream_t st);
-cudaError_t launch_trace_rays(const SceneDev &S, const PreTri *pre, const float *o3, const float *d3,
+cudaError_t launch_trace_rays(const SceneDev &S, const PreSet &pre, const float *o3, const float *d3,
 							  const unsigned char *mask, int n, bool shared, int *triId, float *t, float *bary,
 							  cudaStream_t st);
-cudaError_t launch_trace_shadow(const SceneDev &S, const PreTri *pre, const float origin[3], const float *d3, float *tmax,
+cudaError_t launch_trace_shadow(const SceneDev &S, const PreSet &pre, const float origin[3], const float *d3, float *tmax,
 								int n, cudaStream_t st);
-cudaError_t launch_raytrace(const SceneDev &S, const PreTri *pre, const float *o3, const float *d3,
+cudaError_t launch_raytrace(const SceneDev &S, const PreSet &pre, const float *o3, const float *d3,
 							const unsigned char *mask, int n, bool shared, float *rgb3, cudaStream_t st);
-cudaError_t launch_render(const SceneDev &S, const PreTri *pre, const RayGenParams &g, int W, int H, const int4 *packets,
+cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, const int4 *packets,
 						  int nPackets, unsigned char *out, size_t pitch, cudaStream_t st);
 
 }  // namespace snl

@@ -43,6 +43,8 @@ struct PreCacheEntry {
 	float origin[3];
 	bool valid = false;
 	DevBuf<PreTri> buf;
+	DevBuf<GpuNode> nodes;
+	PreSet set() const { return PreSet{buf.ptr, nodes.ptr}; }
 };
 
 }  // namespace snl
@@ -68,7 +70,7 @@ struct snl_scene {
 	snl::DevBuf<int> dTriMat;
 	int nTriMat = 0;
 	snl::DevBuf<snl::DevMaterial> dMats;
-	int nMats = 0;
+	int nMats = 0, hasUber = 0;
 	snl::DevBuf<snl::DevTexture> dTexs;
 	std::vector<snl::DevBuf<unsigned char>> dTexData;
 
