@@ -1,0 +1,76 @@
+"""CPU tests pinning oracle/snail_oracle.c (plain-C per-ray restatement) against the committed goldens, which are
+outputs of the reference itself (tools/make_golden.py). The scene is fed in the reference layouts produced by the host
+ingest + builder (whose bit-identity with the reference's builder is pinned by tests/test_golden_cpu.py)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import DATA, GOLDEN, ROOT
+
+MANIFEST = json.load(open(os.path.join(GOLDEN, "manifest.json")))
+STAGES = {"simple_nolight": ({}, False), "depth": ({1: 1}, False), "simple_light": ({}, True),
+          "full_light": ({6: 1}, True), "whitted": ({6: 1, 7: 1}, True)}
+
+
+def find(sub, name):
+    for d in (os.path.join(ROOT, "assets"), os.path.join(ROOT, "oracle", "_ref")):
+        p = os.path.join(d, sub, name)
+        if os.path.exists(p):
+            return p
+    pytest.skip(f"{sub}/{name}: scene assets not present")
+
+
+def load(sb, name):
+    import snail_oracle as O
+    c = MANIFEST["cases"][name]
+    g = np.load(os.path.join(GOLDEN, name + ".npz"))
+    mtl = os.path.join(DATA, c["mtl"]) if c["mtl"] else None
+    texdir = (os.path.dirname(find("data", "347.png")) + "/") if c["mtl"] else None
+    hs = sb.HostScene(find("scenes", c["obj"]), mtl, texdir)
+    nodes, tris, shtris, matids = hs.bvh()
+    return c, g, O.OracleScene(nodes, tris, shtris, matids, hs.materials(), hs.textures())
+
+
+@pytest.mark.parametrize("name", list(MANIFEST["cases"]))
+def test_c_oracle_hits_vs_golden(sb, name):
+    c, g, orc = load(sb, name)
+    W, H = int(g["size"][0]), int(g["size"][1])
+    tri, t, bary = orc.trace_primary(g["camera"], W, H)
+    same = tri == g["tri"]
+    # per-ray walk vs the reference's packet walk: ids may differ only on exact-t ties / silhouette edges
+    assert (~same).sum() <= max(2, 1e-3 * W * H)
+    for y, x in np.argwhere(~same):
+        tie = np.isfinite(t[y, x]) and np.isfinite(g["t"][y, x]) and abs(t[y, x] - g["t"][y, x]) <= 1e-4 * abs(g["t"][y, x])
+        edge = any(min(abs(b[0]), abs(b[1]), abs(1 - b[0] - b[1])) < 1e-4
+                   for i, b in ((tri[y, x], bary[y, x]), (g["tri"][y, x], g["bary"][y, x])) if i >= 0)
+        assert tie or edge
+    hit = same & (tri >= 0)
+    assert (t[hit] == g["t"][hit]).all() and (bary[hit] == g["bary"][hit]).all()  # bit-identical hit records
+    for mask, key in ((None, "ray"), (g["ray_mask"], "rayM")):
+        tri, t, bary = orc.trace_rays(g["ray_o"], g["ray_d"], mask)
+        same = tri == g[key + "_tri"]
+        assert (~same).sum() <= 2
+        hit = same & (tri >= 0)
+        assert (t[hit] == g[key + "_t"][hit]).all()
+    out = orc.trace_shadow(g["sh_origin"], g["ray_d"], g["sh_tmax"])
+    assert (np.isneginf(out) != np.isneginf(g["sh_out"])).sum() <= 1
+    orc.close()
+
+
+@pytest.mark.parametrize("name", list(MANIFEST["cases"]))
+def test_c_oracle_frames_vs_golden(sb, name):
+    c, g, orc = load(sb, name)
+    W, H = int(g["size"][0]), int(g["size"][1])
+    for stage, (gv, lit) in STAGES.items():
+        orc.set_gvals(gv)
+        orc.set_lights([g["light"]] if lit else [])
+        img, st = orc.render(g["camera"], W, H)
+        err = np.abs(img.astype(np.int16) - g["img_" + stage].astype(np.int16)).max(axis=2)
+        if stage != "depth":
+            err[g["undef_simple"]] = 0
+        frac = float((err <= 1).mean())
+        assert frac >= 0.999, (stage, frac)
+        assert abs(st["rays"] - c["rays"][stage]) <= max(int(g["undef_simple"].sum()), 0.002 * c["rays"][stage]), stage
+    orc.close()
