@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 
@@ -278,6 +279,13 @@ snl_scene *snl_scene_create(int device) {
 	}
 	snl_scene *s = new snl_scene;
 	s->device = device;
+	cudaDeviceGetAttribute(&s->smCount, cudaDevAttrMultiProcessorCount, device);
+	if(s->smCount <= 0)
+		s->smCount = 148;
+	// SNL_WAVEFRONT=1 selects the queue-driven pipeline of snl_wavefront.cu for frames with the bounce; measured
+	// slower than the fused kernel on every scene tried, so the fused k_render is the default
+	const char *wfEnv = getenv("SNL_WAVEFRONT");
+	s->fused = !(wfEnv && wfEnv[0] == '1');
 	bool ok = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking) == cudaSuccess &&
 			  cudaEventCreate(&s->ev0) == cudaSuccess && cudaEventCreate(&s->ev1) == cudaSuccess &&
 			  s->dCounters.reserve(1) == cudaSuccess;
@@ -314,6 +322,18 @@ void snl_scene_destroy(snl_scene *s) {
 	for(auto &b : s->dScratch)
 		b.release();
 	s->dPackets.release();
+	s->wfRayO.release();
+	s->wfRayD.release();
+	s->wfHit1.release();
+	s->wfSt0.release();
+	s->wfSt1.release();
+	s->wfSdir.release();
+	s->wfSdot.release();
+	s->wfRq.release();
+	s->wfSq.release();
+	s->wfOccl.release();
+	s->wfCount.release();
+	s->wfLightSets.release();
 	for(void *p : s->peerFrames)
 		cudaIpcCloseMemHandle(p);
 	for(void *p : s->ownedFrames)
@@ -695,6 +715,44 @@ static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, cons
 	if(tiles) {
 		SNL_TRY(ensure_packets(s, tiles, nTiles, W, H));
 		packets = s->dPackets.ptr;
+	}
+	const int nPk = packets ? s->nPackets : ((W + 15) / 16) * ((H + 15) / 16);
+	if(S.gvRefl && !S.gvDepth && !s->fused && nPk > 0) {
+		// reflection bounce: wavefront pipeline with queue-driven persistent traversal of the incoherent rays
+		const size_t NL = (size_t)nPk * kPacket, nl = std::max<size_t>(S.nLights, 1);
+		SNL_REQUIRE(NL * nl < 0xffffffffull, SNL_ERR_UNSUPPORTED, "frame too large for 32-bit ray ids");
+		WfBuffers B;
+		SNL_CUDA(s->wfRayO.reserve(NL));
+		SNL_CUDA(s->wfRayD.reserve(NL));
+		SNL_CUDA(s->wfHit1.reserve(NL));
+		SNL_CUDA(s->wfSt0.reserve(4 * NL));
+		SNL_CUDA(s->wfSt1.reserve(2 * NL));
+		SNL_CUDA(s->wfSdir.reserve(nl * NL));
+		SNL_CUDA(s->wfSdot.reserve(nl * NL));
+		SNL_CUDA(s->wfRq.reserve(NL));
+		SNL_CUDA(s->wfSq.reserve(nl * NL));
+		SNL_CUDA(s->wfOccl.reserve(NL));
+		SNL_CUDA(s->wfCount.reserve(4));
+		SNL_CUDA(s->wfLightSets.reserve(kMaxLights));
+		SNL_CUDA(cudaMemcpyAsync(s->wfLightSets.ptr, S.lightPre, sizeof(S.lightPre), cudaMemcpyHostToDevice, s->stream));
+		B.rayO = s->wfRayO.ptr;
+		B.rayD = s->wfRayD.ptr;
+		B.hit1 = s->wfHit1.ptr;
+		B.st0 = s->wfSt0.ptr;
+		B.st1 = s->wfSt1.ptr;
+		B.sdir = s->wfSdir.ptr;
+		B.sdot = s->wfSdot.ptr;
+		B.rq = s->wfRq.ptr;
+		B.sq = s->wfSq.ptr;
+		B.occl = s->wfOccl.ptr;
+		B.qcount = s->wfCount.ptr;
+		B.lightSets = s->wfLightSets.ptr;
+		B.NL = (unsigned)NL;
+		int launches = 0;
+		SNL_CUDA(launch_render_wavefront(S, s->originPre.set(), g, W, H, packets, s->nPackets, B, s->smCount, dOut, pitch,
+										 s->stream, &launches));
+		s->launches += launches;
+		return SNL_OK;
 	}
 	SNL_CUDA(launch_render(S, s->originPre.set(), g, W, H, packets, s->nPackets, dOut, pitch, s->stream));
 	s->launches++;

@@ -480,46 +480,75 @@ __device__ __forceinline__ void shade_block(const SceneDev &S, bool sel, const H
 	}
 }
 
-// Scene::TraceLight for one lane (src/scene_trace.cpp:523-601). Returns true when a shadow ray was cast.
-__device__ __forceinline__ bool trace_light(const SceneDev &S, int li, bool sel, const Sample &s, float &ldr, float &ldg,
-											float &ldb, float &lsr, float &lsg, float &lsb, TravCount &tc) {
-	if(!sel)
-		return false;
-	const DevLight &L = S.lights[li];
-	float lx = s.px - L.pos[0], ly = s.py - L.pos[1], lz = s.pz - L.pos[2];
+// Scene::TraceLight (src/scene_trace.cpp:523-601) in two halves so that the shadow ray between them can be traced
+// either inline (trace_light) or by the queued traversal kernel of the wavefront pipeline.
+// light_setup: direction / distance / N.L of the shadow ray; returns true when the reference casts one (N.L > 0).
+__device__ __forceinline__ bool light_setup(const DevLight &L, float px, float py, float pz, float nx, float ny, float nz,
+											float &fx, float &fy, float &fz, float &dot, float &distance) {
+	float lx = px - L.pos[0], ly = py - L.pos[1], lz = pz - L.pos[2];
 	if(lx * lx + ly * ly + lz * lz < 0.0001f) {
 		lx = 0.0f;
 		ly = 1.0f;
 		lz = 0.0f;
 	}
-	const float distance = sqrtf(lx * lx + ly * ly + lz * lz);
+	distance = sqrtf(lx * lx + ly * ly + lz * lz);
 	const float inv = 1.0f / distance;
-	const float fx = lx * inv, fy = ly * inv, fz = lz * inv;
-	const float dot = s.nx * fx + s.ny * fy + s.nz * fz;
-	if(!(dot > 0.0f))
+	fx = lx * inv;
+	fy = ly * inv;
+	fz = lz * inv;
+	dot = nx * fx + ny * fy + nz * fz;
+	return dot > 0.0f;
+}
+
+// light_accumulate: attenuation + diffuse / specular sums of an unoccluded light (:575-598).
+__device__ __forceinline__ void light_accumulate(const DevLight &L, float dot, float distance, float &ldr, float &ldg,
+												 float &ldb, float &lsr, float &lsg, float &lsb) {
+	float atten = distance * L.iRadius;
+	const float x = ((1.0f - atten) * 0.2f + 1.0f / (16.0f * atten * atten)) - 0.0625f;
+	atten = 0.0f > x ? 0.0f : x;  // Max(f32x4(0), x)
+	const float diffMul = dot * atten;
+	float specMul = dot;
+	specMul *= specMul;
+	specMul *= specMul;
+	specMul *= specMul;
+	specMul *= specMul;
+	specMul *= atten;
+	ldr += L.color[0] * diffMul;
+	ldg += L.color[1] * diffMul;
+	ldb += L.color[2] * diffMul;
+	lsr += L.color[0] * specMul;
+	lsg += L.color[1] * specMul;
+	lsb += L.color[2] * specMul;
+}
+
+// Returns true when a shadow ray was cast.
+__device__ __forceinline__ bool trace_light(const SceneDev &S, int li, bool sel, const Sample &s, float &ldr, float &ldg,
+											float &ldb, float &lsr, float &lsg, float &lsb, TravCount &tc) {
+	if(!sel)
+		return false;
+	const DevLight &L = S.lights[li];
+	float fx, fy, fz, dot, distance;
+	if(!light_setup(L, s.px, s.py, s.pz, s.nx, s.ny, s.nz, fx, fy, fz, dot, distance))
 		return false;
 	const float tmax = distance * 0.9999f;
 	const bool occluded = traverse_shadow(S.lightPre[li].nodes, S.lightPre[li].tris, fx, fy, fz, safe_inv(fx), safe_inv(fy),
 										  safe_inv(fz), tmax, tc);
-	if(!occluded && tmax > 0.0f) {
-		float atten = distance * L.iRadius;
-		const float x = ((1.0f - atten) * 0.2f + 1.0f / (16.0f * atten * atten)) - 0.0625f;
-		atten = 0.0f > x ? 0.0f : x;  // Max(f32x4(0), x)
-		const float diffMul = dot * atten;
-		float specMul = dot;
-		specMul *= specMul;
-		specMul *= specMul;
-		specMul *= specMul;
-		specMul *= specMul;
-		specMul *= atten;
-		ldr += L.color[0] * diffMul;
-		ldg += L.color[1] * diffMul;
-		ldb += L.color[2] * diffMul;
-		lsr += L.color[0] * specMul;
-		lsg += L.color[1] * specMul;
-		lsb += L.color[2] * specMul;
-	}
+	if(!occluded && tmax > 0.0f)
+		light_accumulate(L, dot, distance, ldr, ldg, ldb, lsr, lsg, lsb);
 	return true;
+}
+
+// Scene::TraceReflection's ray (src/scene_trace.cpp:603-614): r = d - 2 (N.d) N, origin = P + r * 0.001
+__device__ __forceinline__ void reflection_ray(const Sample &s, float dx, float dy, float dz, float &rx, float &ry, float &rz,
+											   float &rox, float &roy, float &roz) {
+	const float dot = s.nx * dx + s.ny * dy + s.nz * dz;
+	const float dd = dot + dot;
+	rx = dx - s.nx * dd;
+	ry = dy - s.ny * dd;
+	rz = dz - s.nz * dd;
+	rox = s.px + rx * 0.001f;
+	roy = s.py + ry * 0.001f;
+	roz = s.pz + rz * 0.001f;
 }
 
 struct PacketCounts {
@@ -566,10 +595,8 @@ __device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet or
 		// selector.All() of the packet (src/scene_trace.cpp:615-617) picks RayGroup<0,0> or <0,1> for the bounce; only
 		// UberMaterial::Shade_ looks at it, so the CTA-wide vote is skipped for scenes without one
 		const bool all = S.hasUber ? (bool)__syncthreads_and(sel) : true;
-		const float dot = s.nx * dx + s.ny * dy + s.nz * dz;
-		const float dd = dot + dot;
-		const float rx = dx - s.nx * dd, ry = dy - s.ny * dd, rz = dz - s.nz * dd;
-		const float rox = s.px + rx * 0.001f, roy = s.py + ry * 0.001f, roz = s.pz + rz * 0.001f;
+		float rx, ry, rz, rox, roy, roz;
+		reflection_ray(s, dx, dy, dz, rx, ry, rz, rox, roy, roz);
 		float cr = 0.0f, cg = 0.0f, cb = 0.0f;
 		raytrace_lane<1, false>(S, PreSet{nullptr, nullptr}, sel, !all, rox, roy, roz, rx, ry, rz, cr, cg, cb, pc, tc);
 		if(sel) {

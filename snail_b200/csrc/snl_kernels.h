@@ -9,6 +9,7 @@ namespace snl {
 
 struct SceneDev;
 struct PreSet;
+struct WfBuffers;
 
 cudaError_t launch_pretransform(const GenTri *gtris, int nTris, const GpuNode *nodes, int nNodes, const float origin[3],
 								PreTri *out, GpuNode *outNodes, cudaStream_t st);
@@ -23,5 +24,10 @@ cudaError_t launch_raytrace(const SceneDev &S, const PreSet &pre, const float *o
 							const unsigned char *mask, int n, bool shared, float *rgb3, cudaStream_t st);
 cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, const int4 *packets,
 						  int nPackets, unsigned char *out, size_t pitch, cudaStream_t st);
+
+// Wavefront form of launch_render for frames with the reflection bounce (snl_wavefront.cu). *launches = kernels issued.
+cudaError_t launch_render_wavefront(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H,
+									const int4 *packets, int nPackets, const WfBuffers &B, int persistentCtas,
+									unsigned char *out, size_t pitch, cudaStream_t st, int *launches);
 
 }  // namespace snl

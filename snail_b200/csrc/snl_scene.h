@@ -91,4 +91,12 @@ struct snl_scene {
 	uint64_t launches = 0;
 
 	std::vector<void *> ownedFrames, peerFrames;  // snl_frame_create / snl_frame_open
+
+	// wavefront pipeline (snl_wavefront.cu): per-lane state + ray queues, grow-only
+	snl::DevBuf<snl::Float4> wfRayO, wfRayD, wfHit1, wfSt0, wfSt1, wfSdir;
+	snl::DevBuf<float2> wfSdot;
+	snl::DevBuf<unsigned> wfRq, wfSq, wfOccl, wfCount;
+	snl::DevBuf<snl::PreSet> wfLightSets;
+	int smCount = 0;
+	int fused = 1;  // 0 (SNL_WAVEFRONT=1): wavefront pipeline for frames with the reflection bounce
 };

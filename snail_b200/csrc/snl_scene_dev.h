@@ -31,4 +31,23 @@ struct SceneDev {
 	Counters *counters;
 };
 
+// Wavefront pipeline state for one frame (snl_wavefront.cu). NL = packets * 256 lanes; arrays are lane-indexed
+// (lane = packet * 256 + thread) unless noted, so the shading kernels keep the reference's packet / quad structure
+// while the traversal kernels pull rays from compacted queues.
+struct WfBuffers {
+	Float4 *rayO;    // reflection ray origin.xyz, w = 1 when the primary ray hit (sel0)
+	Float4 *rayD;    // reflection ray direction.xyz
+	Float4 *hit1;    // reflection hit {dist, obj (int bits), bu, bv}
+	Float4 *st0;     // [4 * NL] level-0 state planes: diffuse.rgb | specular.rgb | lightDiffuse.rgb | lightSpecular.rgb
+	Float4 *st1;     // [2 * NL] level-1 state: {diffuse.rgb, sel1} {specular.rgb, 0}
+	Float4 *sdir;    // [nLights * NL] level-1 shadow ray {dir.xyz, tmax}
+	float2 *sdot;    // [nLights * NL] {N.L, distance} of that ray (N.L <= 0: not cast)
+	unsigned *rq;    // compacted lane ids of the reflection rays
+	unsigned *sq;    // compacted (light * NL + lane) ids of the level-1 shadow rays
+	unsigned *occl;  // bit `light` set: that level-1 shadow ray is occluded
+	unsigned *qcount;  // [0] #rq  [1] #sq  [2] rq fetch cursor  [3] sq fetch cursor
+	const PreSet *lightSets;  // device copy of SceneDev::lightPre (dynamically indexed by the shadow kernel)
+	unsigned NL;
+};
+
 }  // namespace snl

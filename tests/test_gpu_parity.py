@@ -313,3 +313,32 @@ def test_render_sponza_like_vs_oracle(sb):
         print(f"sponza_like {gv}: <=1: {ok1*100:.4f}% identical {exact*100:.4f}% max {mx} rays gpu {st_g['rays']} ref {st_r['rays']}")
         assert ok1 >= 0.999
         assert abs(st_g["rays"] - st_r["rays"]) <= 0.002 * st_r["rays"]
+
+
+@pytest.mark.parametrize("name,inside,W,H", [("feline", False, 640, 360), ("box", True, 320, 200), ("barracks", False, 648, 360)])
+def test_wavefront_pipeline_equals_fused_kernel(sb, name, inside, W, H, monkeypatch):
+    """The queue-driven wavefront form of Render() (snl_wavefront.cu, used when gVals[7] is on) against the
+    single-kernel k_render (the default; SNL_WAVEFRONT=1 selects the pipeline): same device functions, so frames and ray counts must be identical -
+    full frame and a tile list."""
+    import os
+    mtl = os.path.join(DATA, "barracks.mtl") if name == "barracks" else None
+    path = scene_path(name)
+    frames = {}
+    for fused in ("1", "0"):
+        monkeypatch.setenv("SNL_WAVEFRONT", "0" if fused == "1" else "1")
+        sc = sb.Scene(0)
+        sc.load_obj(path, mtl, TEXDIR + "/" if mtl else None)
+        cam, light = sb.bench_camera(*sc.bbox(), inside=inside)
+        light2 = sb.Light((light.pos[0] + 1.0, light.pos[1] + 2.0, light.pos[2]), (0.5, 0.8, 1.0), light.radius)
+        sc.set_options({6: 1, 7: 1})
+        sc.set_lights([light, light2])
+        full, st = sc.render(cam, W, H)
+        tiles = [(x, y, 16, min(64, H - y)) for y in range(0, H, 64) for x in range(0, W - 15, 16)][::3]
+        part = np.zeros((H, W, 3), np.uint8)
+        _, st_t = sc.render(cam, W, H, tiles=tiles, out=part)
+        frames[fused] = (full, st, part, st_t)
+        sc.close()
+    a, b = frames["1"], frames["0"]
+    assert (a[0] == b[0]).all() and (a[2] == b[2]).all()
+    for k in ("rays", "primary", "shadow", "reflection", "reflection_shadow"):
+        assert a[1][k] == b[1][k] and a[3][k] == b[3][k], k
