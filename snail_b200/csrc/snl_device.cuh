@@ -18,6 +18,20 @@ namespace snl {
 __device__ __forceinline__ float4 ldg4(const Float4 *p) { return __ldg(reinterpret_cast<const float4 *>(p)); }
 __device__ __forceinline__ int4 ldg4(const Int4 *p) { return __ldg(reinterpret_cast<const int4 *>(p)); }
 
+// 256-bit read-only load (LDG.E.ENL2.256.CONSTANT on sm_100a): `p` must be 32-byte aligned. Divergent lanes pay the
+// L1 one wavefront per distinct line and load instruction, so a 64-byte record costs two of these instead of four
+// 128-bit loads.
+__device__ __forceinline__ void ldg8(const void *p, float4 &lo, float4 &hi) {
+#ifndef SNL_NO_LDG256
+	asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+				 : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w)
+				 : "l"(p));
+#else
+	lo = __ldg(reinterpret_cast<const float4 *>(p));
+	hi = __ldg(reinterpret_cast<const float4 *>(p) + 1);
+#endif
+}
+
 #ifdef SNL_COUNTERS
 #define SNL_COUNT(var) (++(var))
 #else
@@ -93,7 +107,9 @@ __device__ __forceinline__ void tri_nearest_pre(const PreTri *__restrict__ t, in
 // Triangle::Collide(Context<0,*>&) per ray (src/triangle.cpp:29-37,41-61): per-ray origin.
 __device__ __forceinline__ void tri_nearest_gen(const GenTri *__restrict__ t, int idx, float ox, float oy, float oz,
 												float dx, float dy, float dz, Hit &h) {
-	const float4 ta = ldg4(&t->a), tba = ldg4(&t->ba), tca = ldg4(&t->ca), tn = ldg4(&t->n);
+	float4 ta, tba, tca, tn;
+	ldg8(&t->a, ta, tba);
+	ldg8(&t->ca, tca, tn);
 	const float det = dx * tn.x + dy * tn.y + dz * tn.z;
 	const float tx = ox - ta.x, ty = oy - ta.y, tz = oz - ta.z;
 	// tvec0 = ba ^ tvec, tvec1 = tvec ^ ca   (veclib/vec3.h:101-106)
@@ -134,6 +150,17 @@ enum { kSentinel = 0x7fffffff };
 // One step of the walk after the two box tests of the node at `cur`: go to the nearer hit child (push the farther), or
 // pop; a leaf reached while none is parked gets parked and the walk continues with the next stack entry. stack[-1]
 // reads (sp == 0 when tos is the sentinel) cannot happen: the sentinel ends the walk before it would be popped twice.
+#ifdef SNL_STEP_TOS
+#define SNL_STACK_DECL()        \
+	int stackMem[kStack + 1];   \
+	int *const stack = stackMem + 1; \
+	int sp = 0;                 \
+	int tos = kSentinel
+#define SNL_POP(dst)        \
+	do {                    \
+		dst = tos;          \
+		tos = stack[--sp];  \
+	} while(0)
 #define SNL_TRAVERSE_STEP()                                   \
 	do {                                                      \
 		const bool both_ = h0 && h1, any_ = h0 || h1;         \
@@ -154,15 +181,40 @@ enum { kSentinel = 0x7fffffff };
 		}                                                     \
 		cur = next_;                                          \
 	} while(0)
+#else
+// Default: plain stack in local memory, [0] = sentinel. Fewer instructions per step than the register-cached top
+// (SNL_STEP_TOS, kept for the wavefront kernels), one more dependent LDL on a double pop: 0.5 % faster on B200.
+#define SNL_STACK_DECL()   \
+	int stack[kStack + 1]; \
+	stack[0] = kSentinel;  \
+	int sp = 1
+#define SNL_POP(dst) dst = stack[--sp]
+#define SNL_TRAVERSE_STEP()                                   \
+	do {                                                      \
+		const bool both_ = h0 && h1, any_ = h0 || h1;         \
+		const bool swap_ = lmin1 < lmin0;                     \
+		int next_ = both_ ? (swap_ ? l1 : l0) : (h0 ? l0 : l1); \
+		if(both_)                                             \
+			stack[sp++] = swap_ ? l0 : l1;                    \
+		if(!any_)                                             \
+			next_ = stack[--sp];                              \
+		if(next_ < 0 && leaf == 0) {                          \
+			leaf = next_;                                     \
+			next_ = stack[--sp];                              \
+		}                                                     \
+		cur = next_;                                          \
+	} while(0)
+#endif
 
 // Both children of one inner node. REL: boxes are already relative to the ray origin.
 template <bool REL>
 __device__ __forceinline__ void node_test(const GpuNode *__restrict__ n, float ox, float oy, float oz, float ix, float iy,
 										  float iz, float dist, bool &h0, bool &h1, float &lmin0, float &lmin1, int &l0, int &l1) {
-	const float4 b0 = ldg4(&n->b0), b1 = ldg4(&n->b1), bz = ldg4(&n->bz);
-	const int2 link = __ldg(reinterpret_cast<const int2 *>(&n->link));
-	l0 = link.x;
-	l1 = link.y;
+	float4 b0, b1, bz, lk;
+	ldg8(&n->b0, b0, b1);
+	ldg8(&n->bz, bz, lk);
+	l0 = __float_as_int(lk.x);
+	l1 = __float_as_int(lk.y);
 	if(REL) {
 		h0 = box_test_rel(b0.x, b0.y, b0.z, b0.w, bz.x, bz.y, ix, iy, iz, dist, lmin0);
 		h1 = box_test_rel(b1.x, b1.y, b1.z, b1.w, bz.z, bz.w, ix, iy, iz, dist, lmin1);
@@ -178,11 +230,9 @@ template <bool SHARED>
 __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nodes, const void *__restrict__ tris,
 												 float ox, float oy, float oz, float dx, float dy, float dz, float ix,
 												 float iy, float iz, Hit &h, TravCount &tc) {
-	// the top of the stack lives in a register (tos): a pop hands out the next node without waiting for local memory
-	int stackMem[kStack + 1];  // [0] is a guard slot: popping the sentinel reads stack[-1]
-	int *const stack = stackMem + 1;
-	int sp = 0;
-	int tos = kSentinel;
+	// default: the top of the stack lives in a register (tos), a pop hands out the next node without waiting for local
+	// memory; stack[-1] is a guard slot because popping the sentinel reads it
+	SNL_STACK_DECL();
 	int cur = 0;
 	while(cur != kSentinel) {
 		int leaf = 0;  // parked leaf link (< 0), 0 = none
@@ -210,10 +260,8 @@ __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nod
 				}
 			}
 			leaf = cur;
-			if(cur < 0) {
-				cur = tos;
-				tos = stack[--sp];
-			}
+			if(cur < 0)
+				SNL_POP(cur);
 		}
 	}
 }
@@ -223,10 +271,7 @@ __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nod
 // Origin = light position: nodes are that light's translated boxes, triangles its PreTri records.
 __device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ nodes, const PreTri *__restrict__ tris, float dx,
 												float dy, float dz, float ix, float iy, float iz, float dist, TravCount &tc) {
-	int stackMem[kStack + 1];  // [0] is a guard slot: popping the sentinel reads stack[-1]
-	int *const stack = stackMem + 1;
-	int sp = 0;
-	int tos = kSentinel;
+	SNL_STACK_DECL();
 	int cur = 0;
 	bool occluded = false;
 	while(cur != kSentinel) {
@@ -260,10 +305,8 @@ __device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ node
 				break;
 			}
 			leaf = cur;
-			if(cur < 0) {
-				cur = tos;
-				tos = stack[--sp];
-			}
+			if(cur < 0)
+				SNL_POP(cur);
 		}
 	}
 	return occluded;
@@ -424,10 +467,8 @@ __device__ __forceinline__ void shade_block(const SceneDev &S, bool sel, const H
 		float4 w0, w1, w2, w3;
 		if(sel) {
 			const float4 *sp = reinterpret_cast<const float4 *>(S.shtris + obj);
-			w0 = __ldg(sp + 0);  // uv0.x uv0.y uv1.x uv1.y
-			w1 = __ldg(sp + 1);  // uv2.x uv2.y n0.x n0.y
-			w2 = __ldg(sp + 2);  // n0.z n1.x n1.y n1.z
-			w3 = __ldg(sp + 3);  // n2.x n2.y n2.z mat
+			ldg8(sp, w0, w1);      // uv0.x uv0.y uv1.x uv1.y | uv2.x uv2.y n0.x n0.y
+			ldg8(sp + 2, w2, w3);  // n0.z n1.x n1.y n1.z     | n2.x n2.y n2.z mat
 			const int smat = __float_as_int(w3.w);
 			const int mi = smat & 0x7fffffff;
 			matId = mi < S.nTriMat ? S.triMat[mi] : -1;
@@ -594,7 +635,11 @@ __device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet or
 	if(LEVEL == 0 && S.gvRefl) {  // src/scene_trace.cpp:454-466, TraceReflection :603-618
 		// selector.All() of the packet (src/scene_trace.cpp:615-617) picks RayGroup<0,0> or <0,1> for the bounce; only
 		// UberMaterial::Shade_ looks at it, so the CTA-wide vote is skipped for scenes without one
+#ifdef SNL_EXPERIMENT_NOBAR
+		const bool all = true;
+#else
 		const bool all = S.hasUber ? (bool)__syncthreads_and(sel) : true;
+#endif
 		float rx, ry, rz, rox, roy, roz;
 		reflection_ray(s, dx, dy, dz, rx, ry, rz, rox, roy, roz);
 		float cr = 0.0f, cg = 0.0f, cb = 0.0f;

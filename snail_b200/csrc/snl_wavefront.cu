@@ -14,6 +14,8 @@
 //   k_wf_resolve   per packet : level-1 lights, reflection blend (scene_trace.cpp:454-466), compose, ConvColor, store
 //
 // Arithmetic is the same device functions as the fused kernel (snl_device.cuh), so the frame is bit-identical to it.
+// this file keeps its own register-cached stack top
+#define SNL_STEP_TOS
 #include "snl_device.cuh"
 #include "snl_kernels.h"
 
