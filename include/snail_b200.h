@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define SNL_ABI_VERSION 1
+#define SNL_ABI_VERSION 2
 
 typedef enum snl_status {
 	SNL_OK = 0,
@@ -52,7 +52,7 @@ typedef enum snl_material_kind {
 	SNL_MAT_SIMPLE = 0,     /* shading::SimpleMaterial<true>   src/shading/simple_material.h:13-30 */
 	SNL_MAT_UBER = 1,       /* shading::UberMaterial           src/shading/uber_material.h:12-31   */
 	SNL_MAT_TEX = 2,        /* shading::TexMaterial<true>      src/shading/tex_material.h:14-34    */
-	SNL_MAT_TRANSPARENT = 3 /* shading::TransparentMaterial<1> (not implemented on the device yet) */
+	SNL_MAT_TRANSPARENT = 3 /* shading::TransparentMaterial<1> src/shading/transparent_material.h:15-41 */
 } snl_material_kind;
 
 /* Material::flags (src/shading/material.h:14-19) */
@@ -64,7 +64,8 @@ typedef struct snl_material {
 	float color[3];    /* Simple: colour; Uber: diffuse AFTER the x/z swap of uber_material.cpp:11 */
 	float specular[3]; /* Uber only */
 	float opacity;     /* Uber: dissolveFactor */
-	int texture;       /* Tex: index into the texture table, else -1 */
+	int texture;       /* Tex, Transparent: index of the colour texture in the texture table, else -1 */
+	int mask_texture;  /* Transparent: index of the opacity texture (map_d; its first channel is the opacity), else -1 */
 } snl_material;
 
 /* RGB8 mip chain laid out as MipmapTexture does (src/mipmap_texture.cpp:298-308): mips stored back to back,
@@ -80,11 +81,12 @@ typedef struct snl_texture {
  * (src/scene_trace.cpp:117,557): every traced primary ray + every shadow ray actually cast + every reflection
  * ray + the reflection pass's shadow rays. */
 typedef struct snl_stats {
-	uint64_t rays;          /* = primary + shadow + reflection + reflection_shadow */
+	uint64_t rays;          /* = primary + shadow + reflection + reflection_shadow + transparency */
 	uint64_t primary;
 	uint64_t shadow;
 	uint64_t reflection;
 	uint64_t reflection_shadow;
+	uint64_t transparency;  /* rays continued behind a transparent hit (TraceTransparency, src/scene_trace.cpp:620-634) */
 	uint64_t node_visits;   /* only counted when the library is built with SNL_COUNTERS */
 	uint64_t tri_tests;     /* idem: 48-byte per-origin triangle records tested */
 	uint64_t gtri_tests;    /* idem: 64-byte general triangle records tested (reflection rays) */
@@ -116,8 +118,8 @@ int snl_scene_set_materials(snl_scene *, const snl_material *mats, int nMats, co
 int snl_scene_set_lights(snl_scene *, const snl_light *lights, int nLights, const float ambient[3]);
 
 /* The global `int gVals[16]` (src/rtbase.cpp:16). Implemented: [1] depth shading, [6] full shading,
- * [7] reflections, [8] rank tint (uses `rank` of snl_render). [5] (stats heat-map) and [9] (4x AA) return
- * SNL_ERR_UNSUPPORTED. */
+ * [7] reflections, [8] rank tint (uses `rank` of snl_render), [9] 2x2 supersampling in snl_render*
+ * (src/render.cpp:71-110). [5] (stats heat-map) returns SNL_ERR_UNSUPPORTED. */
 int snl_set_options(snl_scene *, const int gVals[16]);
 
 /* Host ingest + SAH builder (host side of the path): BaseScene::LoadWavefrontObj

@@ -44,7 +44,7 @@ typedef struct { /* ShTriangle, src/triangle.h:181-230 */
 typedef struct { /* = snl_material (include/snail_b200.h) */
 	int32_t kind, flags;
 	float color[3], specular[3], opacity;
-	int32_t texture;
+	int32_t texture, mask_texture;
 } OMat;
 
 typedef struct { /* = snl_texture */
@@ -68,7 +68,8 @@ typedef struct oracle_scene {
 	float ambient[3];
 	int gVals[16];
 	/* instrumentation of the last call */
-	uint64_t nodeVisits, triTests, rays[4]; /* primary, shadow, reflection, reflection shadow */
+	unsigned char *undefLanes; /* when set: packet_raytrace reports the lanes the reference shades from uninitialised memory */
+	uint64_t nodeVisits, triTests, rays[5]; /* primary, shadow, reflection, reflection shadow, transparency */
 } oracle_scene;
 
 typedef struct { float dist; int obj; float bu, bv; } OHit;
@@ -274,7 +275,7 @@ static void tex_sample(const OTex *T, float tu, float tv, float tdx, float tdy, 
 	}
 }
 
-typedef struct { float p[3], n[3], diff[3], spec[3]; } OSample;
+typedef struct { float p[3], n[3], diff[3], spec[3], opacity; } OSample;
 
 /* mat->Shade (src/shading/{simple,uber,tex}_material.h Shade_) for one lane; matId -1 = Scene::defaultMat */
 static void material_shade(const oracle_scene *s, int matId, int masked, const float d[3], float tu, float tv, float tdx,
@@ -286,7 +287,15 @@ static void material_shade(const oracle_scene *s, int matId, int masked, const f
 		return;
 	}
 	const OMat *m = s->mats + matId;
-	if(m->kind == 2) {
+	if(m->kind == 3) { /* TransparentMaterial<1>::Shade_, src/shading/transparent_material.h:15-41 */
+		float rgb[3], mask[3];
+		tex_sample(s->texs + m->texture, tu, tv, tdx, tdy, rgb);
+		tex_sample(s->texs + m->mask_texture, tu, tv, tdx, tdy, mask);
+		for(int c = 0; c < 3; c++)
+			sm->diff[c] = sm->spec[c] = rgb[c] * dot;
+		sm->opacity = mask[0];
+	}
+	else if(m->kind == 2) {
 		float rgb[3];
 		tex_sample(s->texs + m->texture, tu, tv, tdx, tdy, rgb);
 		for(int c = 0; c < 3; c++)
@@ -297,6 +306,8 @@ static void material_shade(const oracle_scene *s, int matId, int masked, const f
 			sm->diff[c] = m->color[c] * fabsf(dot);
 			sm->spec[c] = (m->kind == 1 && masked) ? m->specular[c] : sm->diff[c]; /* uber_material.h:21-29 */
 		}
+		if(m->kind == 1)
+			sm->opacity = m->opacity; /* dissFactor, uber_material.h:23,28 */
 	}
 }
 
@@ -348,7 +359,7 @@ static int trace_light(oracle_scene *s, const OLight *L, const OSample *sm, floa
 
 /* Sample construction + material evaluation for one 16-lane block (4 quads), src/scene_trace.cpp:139-452 */
 static void shade_block(const oracle_scene *s, const OPacket *pk, int b0, const OHit *hit, const unsigned char *sel,
-						int packetHasMask, OSample *sm) {
+						int packetHasMask, OSample *sm, unsigned char *trans, unsigned char *undef) {
 	int nsel = 0, same = 1, sameMat = 1;
 	int matId[16];
 	float tu[16], tv[16];
@@ -360,12 +371,28 @@ static void shade_block(const oracle_scene *s, const OPacket *pk, int b0, const 
 			x->p[c] = pk->d[i][c] * hit[i].dist + pk->o[i][c]; /* :163 */
 			x->n[c] = x->diff[c] = x->spec[c] = 0.0f;
 		}
+		x->opacity = 1.0f;
+		trans[i] = 0;
 		nsel += sel[i];
 		same &= (sel[i] ? hit[i].obj : 0) == obj0;
 		matId[l] = -1;
 		tu[l] = tv[l] = 0.0f;
 	}
 	const int blockFull = nsel == 16, fast = blockFull && same;
+	/* Reference quirk (src/scene_trace.cpp:240-290 full shading, :410-423 simple shading): lane 0 of a quad supplies
+	 * the quad's triangle; when it is inactive or missed its object reads 0, and the per-lane fix-up skips lanes whose
+	 * own triangle is 0 as "same as lane 0" -> those lanes are shaded from an uninitialised Sample. We shade them
+	 * properly and report them as undefined so that fixtures can exclude them. */
+	int poisoned = 0;
+	for(int q = 0; q < 4; q++)
+		if(!sel[b0 + q * 4])
+			for(int k = 1; k < 4; k++)
+				poisoned |= sel[b0 + q * 4 + k] && hit[b0 + q * 4 + k].obj == 0;
+	/* such a lane keeps matId ~0 and a garbage normal, which also steers block-level decisions (one material for the
+	 * block or not -> masked / unmasked Shade, the list of materials) -> the whole block counts as undefined */
+	if(poisoned)
+		for(int l = 0; l < 16; l++)
+			undef[b0 + l] |= sel[b0 + l];
 	if(s->gVals[6] && s->shtris) {
 		for(int l = 0; l < 16; l++) {
 			const int i = b0 + l;
@@ -413,6 +440,21 @@ static void shade_block(const oracle_scene *s, const OPacket *pk, int b0, const 
 					material_shade(s, matId[l], masked, pk->d[i], tu[l], tv[l], tdx, tdy, sm + i);
 			}
 		}
+		/* transSel (:190,306,347-349): one material for the block -> its fTransparency flag for every lane; else each
+		 * transparent material, in order of first appearance among the selected lanes, OVERWRITES the block's mask
+		 * (`transSel[b4 + q] = mask[q]`), so only the last one keeps its lanes */
+		int last = -1;
+		for(int l = 0; l < 16; l++) {
+			if(!sel[b0 + l] || matId[l] < 0 || !(s->mats[matId[l]].flags & 8))
+				continue;
+			int seen = 0;
+			for(int k = 0; k < l; k++)
+				seen |= sel[b0 + k] && matId[k] == matId[l];
+			if(!seen)
+				last = matId[l];
+		}
+		for(int l = 0; l < 16; l++)
+			trans[b0 + l] = last >= 0 && sel[b0 + l] && matId[l] == last;
 	}
 	else { /* simple shading: geometric normal, default material (:359-452) */
 		for(int l = 0; l < 16; l++) {
@@ -426,14 +468,13 @@ static void shade_block(const oracle_scene *s, const OPacket *pk, int b0, const 
 	}
 }
 
-static void packet_raytrace(oracle_scene *s, const OPacket *pk, int level, int sharedOrigin, int packetHasMask,
-							float out[256][3]) {
-	static _Thread_local OHit hitBuf[2][256];
-	static _Thread_local OSample smBuf[2][256];
-	static _Thread_local unsigned char selBuf[2][256];
-	OHit *hit = hitBuf[level];
-	OSample *sm = smBuf[level];
-	unsigned char *sel = selBuf[level];
+/* level = cache.reflections (1 inside the reflection pass: no further bounce); transp = inside a transparency pass
+ * (only changes which counter the rays go to). Recursive like the reference; buffers live on the stack. */
+static void packet_raytrace_ex(oracle_scene *s, const OPacket *pk, int level, int transp, int sharedOrigin,
+							   int packetHasMask, float out[256][3], unsigned char undef[256]) {
+	OHit hit[256];
+	OSample sm[256];
+	unsigned char sel[256], trans[256];
 	for(int i = 0; i < pk->n; i++) {
 		hit[i].dist = OINF;
 		hit[i].obj = 0;
@@ -442,7 +483,7 @@ static void packet_raytrace(oracle_scene *s, const OPacket *pk, int level, int s
 		if(pk->active[i]) {
 			const float id[3] = {safe_inv(pk->d[i][0]), safe_inv(pk->d[i][1]), safe_inv(pk->d[i][2])};
 			walk_nearest(s, pk->o[i], pk->d[i], id, sharedOrigin, &hit[i]);
-			s->rays[level ? 2 : 0]++;
+			s->rays[transp ? 4 : level ? 2 : 0]++;
 		}
 	}
 	if(s->gVals[1]) { /* depth shading, :128-137 */
@@ -460,11 +501,11 @@ static void packet_raytrace(oracle_scene *s, const OPacket *pk, int level, int s
 		all &= sel[i];
 	}
 	for(int b0 = 0; b0 < pk->n; b0 += 16)
-		shade_block(s, pk, b0, hit, sel, packetHasMask, sm);
+		shade_block(s, pk, b0, hit, sel, packetHasMask, sm, trans, undef);
 
 	if(level == 0 && s->gVals[7]) { /* TraceReflection :603-618, blend :454-466 */
-		static _Thread_local OPacket rp;
-		static _Thread_local float rc[256][3];
+		OPacket rp;
+		float rc[256][3];
 		rp.n = pk->n;
 		for(int i = 0; i < pk->n; i++) {
 			const float *d = pk->d[i], *n = sm[i].n;
@@ -476,11 +517,44 @@ static void packet_raytrace(oracle_scene *s, const OPacket *pk, int level, int s
 			}
 			rp.active[i] = sel[i];
 		}
-		packet_raytrace(s, &rp, 1, 0, !all, rc);
+		unsigned char ru[256] = {0};
+		packet_raytrace_ex(s, &rp, 1, 0, 0, !all, rc, ru);
+		for(int i = 0; i < pk->n; i++)
+			undef[i] |= sel[i] && ru[i];
 		for(int i = 0; i < pk->n; i++)
 			if(sel[i])
 				for(int c = 0; c < 3; c++)
 					sm[i].diff[c] = sm[i].diff[c] + (rc[i][c] - sm[i].diff[c]) * 0.3f;
+	}
+	{ /* transparency pass :468-483, TraceTransparency :620-634 (cache.reflections is NOT bumped: the continued rays
+	   * bounce again on level 0) */
+		int any = 0, allT = 1;
+		for(int i = 0; i < pk->n; i++) {
+			trans[i] = trans[i] && sm[i].opacity < 1.0f;
+			any |= trans[i];
+			allT &= trans[i];
+		}
+		if(any) {
+			OPacket tp;
+			float tcol[256][3];
+			tp.n = pk->n;
+			for(int i = 0; i < pk->n; i++) {
+				const float t = hit[i].dist + 0.001f;
+				for(int c = 0; c < 3; c++) {
+					tp.d[i][c] = pk->d[i][c];
+					tp.o[i][c] = pk->d[i][c] * t + pk->o[i][c];
+				}
+				tp.active[i] = trans[i];
+			}
+			unsigned char tu[256] = {0};
+			packet_raytrace_ex(s, &tp, level, 1, 0, !allT, tcol, tu);
+			for(int i = 0; i < pk->n; i++)
+				undef[i] |= trans[i] && tu[i];
+			for(int i = 0; i < pk->n; i++)
+				if(trans[i])
+					for(int c = 0; c < 3; c++) /* VLerp(a, b, x) = a + (b - a) * x, veclib/vecbase.h:81 */
+						sm[i].diff[c] = tcol[i][c] + (sm[i].diff[c] - tcol[i][c]) * sm[i].opacity;
+		}
 	}
 	for(int i = 0; i < pk->n; i++) {
 		if(s->nLights) {
@@ -495,6 +569,14 @@ static void packet_raytrace(oracle_scene *s, const OPacket *pk, int level, int s
 			for(int c = 0; c < 3; c++)
 				out[i][c] = sm[i].diff[c];
 	}
+}
+
+static void packet_raytrace(oracle_scene *s, const OPacket *pk, int level, int sharedOrigin, int packetHasMask,
+							float out[256][3]) {
+	unsigned char undef[256] = {0};
+	packet_raytrace_ex(s, pk, level, 0, sharedOrigin, packetHasMask, out, undef);
+	if(s->undefLanes)
+		memcpy(s->undefLanes, undef, 256);
 }
 
 /* ---- exported API (bound by oracle/snail_oracle.py) --------------------------------------------------------------- */
@@ -532,8 +614,8 @@ static void reset_counts(oracle_scene *s) {
 	s->nodeVisits = s->triTests = 0;
 	memset(s->rays, 0, sizeof(s->rays));
 }
-/* counts: nodeVisits, triTests, primary, shadow, reflection, reflection shadow */
-void oracle_counts(const oracle_scene *s, uint64_t out[6]) {
+/* counts: nodeVisits, triTests, primary, shadow, reflection, reflection shadow, transparency */
+void oracle_counts(const oracle_scene *s, uint64_t out[7]) {
 	out[0] = s->nodeVisits;
 	out[1] = s->triTests;
 	memcpy(out + 2, s->rays, sizeof(s->rays));
@@ -598,22 +680,51 @@ static unsigned char conv(float c) {
 	return (unsigned char)(int)v;
 }
 
-/* Render() (src/render.cpp:47-211, 214-243): 16x16 packets, BGR8 rows of 3*W bytes */
+/* Render() (src/render.cpp:47-211, 214-243): 16x16 packets, BGR8 rows of 3*W bytes. gVals[9]: each packet is traced
+ * as four packets of the 2W x 2H image and box-filtered with the reference's add order (:71-110). */
+void oracle_render_ex(oracle_scene *s, const float cam[13], int W, int H, unsigned char *out, unsigned char *undefOut);
 void oracle_render(oracle_scene *s, const float cam[13], int W, int H, unsigned char *out) {
+	oracle_render_ex(s, cam, W, H, out, NULL);
+}
+/* undefOut (W*H bytes, may be NULL): 1 where the reference's pixel depends on an uninitialised Sample (see shade_block) */
+void oracle_render_ex(oracle_scene *s, const float cam[13], int W, int H, unsigned char *out, unsigned char *undefOut) {
 	static _Thread_local OPacket pk;
-	static _Thread_local float col[256][3];
+	unsigned char lanes[256], ulanes[256];
+	s->undefLanes = undefOut ? lanes : NULL;
+	static _Thread_local float col[256][3], sub[256][3];
+	const int ss = s->gVals[9] != 0;
 	ORayGen g;
-	raygen_init(cam, W, H, &g);
+	raygen_init(cam, ss ? 2 * W : W, ss ? 2 * H : H, &g);
 	reset_counts(s);
 	for(int y0 = 0; y0 < H; y0 += 16)
 		for(int x0 = 0; x0 < W; x0 += 16) {
 			pk.n = 256;
-			for(int i = 0; i < 256; i++) {
-				raygen_dir(&g, x0, y0, i & 15, i >> 4, pk.d[i]);
-				memcpy(pk.o[i], g.origin, 12);
-				pk.active[i] = 1; /* overhanging lanes are traced too, src/render.cpp:112-115 */
+			for(int k = 0; k < (ss ? 4 : 1); k++) {
+				const int sx = ss ? x0 * 2 + (k & 1) * 16 : x0, sy = ss ? y0 * 2 + (k >> 1) * 16 : y0;
+				for(int i = 0; i < 256; i++) {
+					raygen_dir(&g, sx, sy, i & 15, i >> 4, pk.d[i]);
+					memcpy(pk.o[i], g.origin, 12);
+					pk.active[i] = 1; /* overhanging lanes are traced too, src/render.cpp:112-115 */
+				}
+				packet_raytrace(s, &pk, 0, 1, 0, ss ? sub : col);
+				if(undefOut && !ss)
+					memcpy(ulanes, lanes, 256);
+				if(undefOut && ss)
+					for(int oy = 0; oy < 8; oy++)
+						for(int ox = 0; ox < 8; ox++) {
+							const int i0 = (2 * oy) * 16 + 2 * ox;
+							ulanes[((k >> 1) * 8 + oy) * 16 + (k & 1) * 8 + ox] = lanes[i0] | lanes[i0 + 1] | lanes[i0 + 16] | lanes[i0 + 17];
+						}
+				if(ss)
+					for(int oy = 0; oy < 8; oy++)
+						for(int ox = 0; ox < 8; ox++)
+							for(int c = 0; c < 3; c++) {
+								const float *t0 = &sub[(2 * oy) * 16 + 2 * ox][c], *t1 = &sub[(2 * oy + 1) * 16 + 2 * ox][c];
+								/* (tcolors[q] + tcolors[q + line]) * 0.25, then lane 0 + lane 1 */
+								const float l = (t0[0] + t1[0]) * 0.25f, r = (t0[3] + t1[3]) * 0.25f;
+								col[((k >> 1) * 8 + oy) * 16 + (k & 1) * 8 + ox][c] = l + r;
+							}
 			}
-			packet_raytrace(s, &pk, 0, 1, 0, col);
 			for(int i = 0; i < 256; i++) {
 				const int x = x0 + (i & 15), y = y0 + (i >> 4);
 				if(x < W && y < H) {
@@ -621,7 +732,10 @@ void oracle_render(oracle_scene *s, const float cam[13], int W, int H, unsigned 
 					dst[0] = conv(col[i][2]);
 					dst[1] = conv(col[i][1]);
 					dst[2] = conv(col[i][0]);
+					if(undefOut)
+						undefOut[(size_t)y * W + x] = ulanes[i];
 				}
 			}
 		}
+	s->undefLanes = NULL;
 }

@@ -38,12 +38,13 @@ def lib():
         _lib.oracle_trace_rays.argtypes = [vp, vp, vp, vp, i, i, vp, vp, vp]
         _lib.oracle_trace_shadow.argtypes = [vp, vp, vp, vp, i]
         _lib.oracle_render.argtypes = [vp, vp, i, i, vp]
+        _lib.oracle_render_ex.argtypes = [vp, vp, i, i, vp, vp]
     return _lib
 
 
 class _Mat(C.Structure):
     _fields_ = [("kind", C.c_int), ("flags", C.c_int), ("color", C.c_float * 3), ("specular", C.c_float * 3),
-                ("opacity", C.c_float), ("texture", C.c_int)]
+                ("opacity", C.c_float), ("texture", C.c_int), ("mask_texture", C.c_int)]
 
 
 class _Tex(C.Structure):
@@ -70,6 +71,7 @@ class OracleScene:
             self.mats[n].color = (C.c_float * 3)(*m["color"])
             self.mats[n].specular = (C.c_float * 3)(*m["specular"])
             self.mats[n].opacity, self.mats[n].texture = float(m["opacity"]), int(m["texture"])
+            self.mats[n].mask_texture = int(m.get("mask_texture", -1))
         self.texs = (_Tex * max(len(textures), 1))()
         self._keep = []
         for n, t in enumerate(textures):
@@ -97,9 +99,9 @@ class OracleScene:
         self.L.oracle_set_lights(self.h, _p(a) if a.size else None, a.shape[0])
 
     def counts(self):
-        c = np.zeros(6, np.uint64)
+        c = np.zeros(7, np.uint64)
         self.L.oracle_counts(self.h, _p(c))
-        return dict(zip(("node_visits", "tri_tests", "primary", "shadow", "reflection", "reflection_shadow"),
+        return dict(zip(("node_visits", "tri_tests", "primary", "shadow", "reflection", "reflection_shadow", "transparency"),
                         [int(x) for x in c]))
 
     def trace_primary(self, cam, W, H):
@@ -123,10 +125,12 @@ class OracleScene:
         self.L.oracle_trace_shadow(self.h, _p(o), _p(d), _p(out), out.size)
         return out
 
-    def render(self, cam, W, H):
+    def render(self, cam, W, H, undef=None):
+        """undef: optional (H, W) uint8 array that receives 1 where the reference's pixel depends on an uninitialised
+        Sample (snail_oracle.c shade_block)."""
         cam = np.ascontiguousarray(cam, np.float32)
         img = np.zeros((H, W, 3), np.uint8)
-        self.L.oracle_render(self.h, _p(cam), W, H, _p(img))
+        self.L.oracle_render_ex(self.h, _p(cam), W, H, _p(img), _p(undef))
         c = self.counts()
-        c["rays"] = c["primary"] + c["shadow"] + c["reflection"] + c["reflection_shadow"]
+        c["rays"] = c["primary"] + c["shadow"] + c["reflection"] + c["reflection_shadow"] + c["transparency"]
         return img, c

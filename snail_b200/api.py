@@ -78,7 +78,7 @@ class Light(C.Structure):
 
 class Material(C.Structure):
     _fields_ = [("kind", C.c_int), ("flags", C.c_int), ("color", C.c_float * 3), ("specular", C.c_float * 3),
-                ("opacity", C.c_float), ("texture", C.c_int)]
+                ("opacity", C.c_float), ("texture", C.c_int), ("mask_texture", C.c_int)]
 
 
 class Texture(C.Structure):
@@ -87,7 +87,7 @@ class Texture(C.Structure):
 
 class Stats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("primary", C.c_uint64), ("shadow", C.c_uint64), ("reflection", C.c_uint64),
-                ("reflection_shadow", C.c_uint64), ("node_visits", C.c_uint64), ("tri_tests", C.c_uint64), ("gtri_tests", C.c_uint64),
+                ("reflection_shadow", C.c_uint64), ("transparency", C.c_uint64), ("node_visits", C.c_uint64), ("tri_tests", C.c_uint64), ("gtri_tests", C.c_uint64),
                 ("kernel_ms", C.c_float)]
 
     def as_dict(self):
@@ -195,7 +195,7 @@ class HostScene:
             m = Material()
             self.L.snl_host_scene_material(self.h, n, C.byref(m))
             out.append(dict(kind=m.kind, flags=m.flags, color=tuple(m.color), specular=tuple(m.specular),
-                            opacity=m.opacity, texture=m.texture))
+                            opacity=m.opacity, texture=m.texture, mask_texture=m.mask_texture))
         return out
 
     def textures(self):
@@ -256,6 +256,7 @@ class Scene:
             mats[n].specular = (C.c_float * 3)(*m.get("specular", (0, 0, 0)))
             mats[n].opacity = float(m.get("opacity", 0.0))
             mats[n].texture = int(m.get("texture", -1))
+            mats[n].mask_texture = int(m.get("mask_texture", -1))
         texs = (Texture * max(len(textures), 1))()
         keep = []
         for n, t in enumerate(textures):

@@ -151,7 +151,8 @@ int sync_and_stats(snl_scene *s, snl_stats *stats) {
 		stats->shadow = c.shadow;
 		stats->reflection = c.reflection;
 		stats->reflection_shadow = c.reflection_shadow;
-		stats->rays = c.primary + c.shadow + c.reflection + c.reflection_shadow;
+		stats->transparency = c.transparency;
+		stats->rays = c.primary + c.shadow + c.reflection + c.reflection_shadow + c.transparency;
 		stats->node_visits = c.node_visits;
 		stats->tri_tests = c.tri_tests;
 		stats->gtri_tests = c.gtri_tests;
@@ -222,7 +223,9 @@ int make_scene_dev(snl_scene *s, SceneDev &S) {
 	S.gvFull = s->gVals[6];
 	S.gvRefl = s->gVals[7];
 	S.gvTint = 0;
+	S.gvSuper = s->gVals[9];
 	S.hasUber = s->hasUber;
+	S.hasTransp = s->hasTransp;
 	S.counters = s->dCounters.ptr;
 	return SNL_OK;
 }
@@ -417,10 +420,10 @@ static int upload_materials(snl_scene *s, const snl_material *mats, int nMats, c
 	for(int i = 0; i < nMats; i++) {
 		const snl_material &m = mats[i];
 		SNL_REQUIRE(m.kind >= SNL_MAT_SIMPLE && m.kind <= SNL_MAT_TRANSPARENT, SNL_ERR_INVALID, "material %d: bad kind", i);
-		SNL_REQUIRE(m.kind != SNL_MAT_TRANSPARENT, SNL_ERR_UNSUPPORTED,
-					"material %d: TransparentMaterial is not implemented on the device", i);
-		if(m.kind == SNL_MAT_TEX)
+		if(m.kind == SNL_MAT_TEX || m.kind == SNL_MAT_TRANSPARENT)
 			SNL_REQUIRE(m.texture >= 0 && m.texture < nTex, SNL_ERR_INVALID, "material %d: texture index", i);
+		if(m.kind == SNL_MAT_TRANSPARENT)
+			SNL_REQUIRE(m.mask_texture >= 0 && m.mask_texture < nTex, SNL_ERR_INVALID, "material %d: mask texture index", i);
 	}
 	for(auto &t : s->dTexData)
 		t.release();
@@ -465,14 +468,20 @@ static int upload_materials(snl_scene *s, const snl_material *mats, int nMats, c
 		memcpy(dm[i].specular, mats[i].specular, 12);
 		dm[i].opacity = mats[i].opacity;
 		dm[i].texture = mats[i].texture;
+		dm[i].texture2 = mats[i].mask_texture;
 	}
 	SNL_CUDA(s->dMats.reserve(std::max(1, nMats)));
 	if(nMats)
 		SNL_CUDA(cudaMemcpy(s->dMats.ptr, dm.data(), nMats * sizeof(DevMaterial), cudaMemcpyHostToDevice));
 	s->nMats = nMats;
-	s->hasUber = 0;
-	for(int i = 0; i < nMats; i++)
+	s->hasUber = s->hasTransp = 0;
+	for(int i = 0; i < nMats; i++) {
 		s->hasUber |= mats[i].kind == SNL_MAT_UBER;
+		// transSel needs fTransparency, and survives only where opacity < 1 (src/scene_trace.cpp:472): an Uber
+		// material with d >= 1 (every material of sponza.mtl) can never start a transparency pass
+		if(mats[i].flags & SNL_MATF_TRANSPARENCY)
+			s->hasTransp |= mats[i].kind == SNL_MAT_TRANSPARENT || (mats[i].kind == SNL_MAT_UBER && mats[i].opacity < 1.0f);
+	}
 	return SNL_OK;
 }
 
@@ -494,7 +503,6 @@ int snl_scene_set_lights(snl_scene *s, const snl_light *lights, int nLights, con
 int snl_set_options(snl_scene *s, const int gVals[16]) {
 	SNL_REQUIRE(s && gVals, SNL_ERR_INVALID, "null argument");
 	SNL_REQUIRE(!gVals[5], SNL_ERR_UNSUPPORTED, "gVals[5] (packet statistics heat-map) has no per-ray equivalent");
-	SNL_REQUIRE(!gVals[9], SNL_ERR_UNSUPPORTED, "gVals[9] (4x supersampling) is not implemented yet");
 	memcpy(s->gVals, gVals, sizeof(s->gVals));
 	return SNL_OK;
 }
@@ -710,14 +718,15 @@ static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, cons
 	}
 	SNL_TRY(ensure_pre(s, s->originPre, cam->pos));
 	RayGenParams g;
-	make_raygen(*cam, W, H, g);
+	const int scale = s->gVals[9] ? 2 : 1;  // src/render.cpp:60-62
+	make_raygen(*cam, W * scale, H * scale, g);
 	const int4 *packets = nullptr;
 	if(tiles) {
 		SNL_TRY(ensure_packets(s, tiles, nTiles, W, H));
 		packets = s->dPackets.ptr;
 	}
 	const int nPk = packets ? s->nPackets : ((W + 15) / 16) * ((H + 15) / 16);
-	if(S.gvRefl && !S.gvDepth && !s->fused && nPk > 0) {
+	if(S.gvRefl && !S.gvDepth && !s->fused && !S.hasTransp && !S.gvSuper && nPk > 0) {
 		// reflection bounce: wavefront pipeline with queue-driven persistent traversal of the incoherent rays
 		const size_t NL = (size_t)nPk * kPacket, nl = std::max<size_t>(S.nLights, 1);
 		SNL_REQUIRE(NL * nl < 0xffffffffull, SNL_ERR_UNSUPPORTED, "frame too large for 32-bit ray ids");

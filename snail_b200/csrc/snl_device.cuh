@@ -340,6 +340,7 @@ struct Sample {
 	float nx, ny, nz;  // normal (not normalised when interpolated, src/scene_trace.cpp:204,220,249)
 	float dr, dg, db;  // diffuse
 	float sr, sg, sb;  // specular
+	float opacity;     // set by Uber / Transparent materials only (src/shading.h:23)
 };
 
 __device__ __forceinline__ float quad_min(float v) {
@@ -410,7 +411,21 @@ __device__ __forceinline__ void material_shade(const SceneDev &S, int matId, boo
 		return;
 	}
 	const DevMaterial &m = S.mats[matId];
-	if(m.kind == 2 /* SNL_MAT_TEX */) {
+	if(m.kind == 3 /* SNL_MAT_TRANSPARENT */) {
+		// TransparentMaterial<1>::Shade_ (src/shading/transparent_material.h:15-41): colour texture * (dir | normal),
+		// opacity = x channel of the second texture, both sampled with the same texCoord / texDiff
+		float r, g, b, tr, tg, tb;
+		tex_sample(S.texs[m.texture], tu, tv, tdx, tdy, r, g, b);
+		tex_sample(S.texs[m.texture2], tu, tv, tdx, tdy, tr, tg, tb);
+		s.dr = r * dot;
+		s.dg = g * dot;
+		s.db = b * dot;
+		s.sr = s.dr;
+		s.sg = s.dg;
+		s.sb = s.db;
+		s.opacity = tr;
+	}
+	else if(m.kind == 2 /* SNL_MAT_TEX */) {
 		float r, g, b;
 		tex_sample(S.texs[m.texture], tu, tv, tdx, tdy, r, g, b);
 		s.dr = r * dot;
@@ -425,6 +440,8 @@ __device__ __forceinline__ void material_shade(const SceneDev &S, int matId, boo
 		s.dr = m.color[0] * a;
 		s.dg = m.color[1] * a;
 		s.db = m.color[2] * a;
+		if(m.kind == 1 /* SNL_MAT_UBER */)
+			s.opacity = m.opacity;  // dissFactor, src/shading/uber_material.h:23,28
 		if(m.kind == 1 /* SNL_MAT_UBER */ && masked) {
 			// UberMaterial::Shade_ hasMask branch stores the material's specular colour, the other branch the
 			// diffuse term (src/shading/uber_material.h:21-29)
@@ -442,8 +459,12 @@ __device__ __forceinline__ void material_shade(const SceneDev &S, int matId, boo
 
 // Sample construction + material evaluation of Scene::RayTrace (src/scene_trace.cpp:139-452) for the calling lane;
 // the 16 lanes of a half-warp are one 4-quad block. Must be called by all 32 lanes of the warp.
+// TRANSP: also evaluates transSel for the lane (`trans`): the material has fTransparency and, in a block shaded per
+// material, it is the LAST such material in order of first appearance - `transSel[b4 + q] = mask[q]` overwrites the
+// whole block for every transparent material in turn (src/scene_trace.cpp:190,306,347-349).
+template <bool TRANSP>
 __device__ __forceinline__ void shade_block(const SceneDev &S, bool sel, const Hit &h, float ox, float oy, float oz, float dx,
-											float dy, float dz, bool packetHasMask, Sample &s) {
+											float dy, float dz, bool packetHasMask, Sample &s, bool &trans) {
 	const int lane = threadIdx.x & 31;
 	const int half = lane >> 4;
 	const int obj = sel ? h.obj : 0;
@@ -453,6 +474,8 @@ __device__ __forceinline__ void shade_block(const SceneDev &S, bool sel, const H
 	s.pz = dz * h.dist + oz;
 	s.dr = s.dg = s.db = s.sr = s.sg = s.sb = 0.0f;
 	s.nx = s.ny = s.nz = 0.0f;
+	s.opacity = 1.0f;
+	trans = false;
 
 	const unsigned selB = (__ballot_sync(SNL_FULL, sel) >> (half * 16)) & 0xffffu;
 	const int obj0 = __shfl_sync(SNL_FULL, obj, half * 16);
@@ -510,6 +533,17 @@ __device__ __forceinline__ void shade_block(const SceneDev &S, bool sel, const H
 		const bool masked = fast ? packetHasMask : !(blockFull && sameMatB == 0xffffu);
 		if(sel)
 			material_shade(S, matId, masked, dx, dy, dz, tu, tv, tdx, tdy, s);
+		if(TRANSP) {
+			const bool isT = sel && matId >= 0 && (S.mats[matId].flags & 8 /* fTransparency */);
+			// lowest lane of the block shaded with my material = its place in the reference's matIds[] list
+			const unsigned peers = __match_any_sync(SNL_FULL, sel ? matId : -2 - lane) & (selB << (half * 16));
+			int key = isT ? __ffs(peers) : 0;
+			int best = key;
+#pragma unroll
+			for(int o = 8; o; o >>= 1)
+				best = max(best, __shfl_xor_sync(SNL_FULL, best, o));
+			trans = isT && key == best;
+		}
 	}
 	else if(sel) {
 		// simple shading: geometric normal, default material (src/scene_trace.cpp:359-452)
@@ -593,16 +627,93 @@ __device__ __forceinline__ void reflection_ray(const Sample &s, float dx, float 
 }
 
 struct PacketCounts {
-	unsigned primary, shadow, reflection, reflection_shadow;
+	unsigned primary, shadow, reflection, reflection_shadow, transparency;
+	int voteGen;  // packet votes taken so far (PacketVote), uniform over the CTA
 };
 
-// Scene::RayTrace for the calling lane (src/scene_trace.cpp:92-520). LEVEL 0 = the caller's rays, LEVEL 1 = the
-// reflection pass (cache.reflections == 1: no further bounce). All 256 threads of the CTA must call it.
-template <int LEVEL, bool SHARED>
-__device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet originPre, bool active,
-											  bool packetHasMask, float ox, float oy, float oz, float dx, float dy,
-											  float dz, float &outr, float &outg, float &outb, PacketCounts &pc,
-											  TravCount &tc) {
+// selector.All() of a packet without a CTA barrier. The verdict is only consumed after the NEXT traversal (it picks
+// RayGroup<0,0> or <0,1> for the reflection pass, which only UberMaterial::Shade_ can tell apart), so a warp posts its
+// share when its primary rays are done and goes on; the reader spins only if another warp has not posted yet - by
+// then it practically always has. Generation-stamped, so it needs no reset between votes: a warp can be at most one
+// vote ahead of the slowest reader. packet_vote_init() once per kernel (shared memory starts undefined).
+struct PacketVote {
+	int arrived;
+	int notAllGen[4];
+};
+__device__ __forceinline__ PacketVote &packet_vote_state() {
+	__shared__ PacketVote v;
+	return v;
+}
+__device__ __forceinline__ void packet_vote_init() {
+	PacketVote &v = packet_vote_state();
+	if(threadIdx.x == 0) {
+		v.arrived = 0;
+		v.notAllGen[0] = v.notAllGen[1] = v.notAllGen[2] = v.notAllGen[3] = 0;
+	}
+	__syncthreads();
+}
+// All 32 lanes of every warp of the CTA call it, the same number of times. Returns the generation to ask about.
+__device__ __forceinline__ int packet_vote_post(bool pred, PacketCounts &pc) {
+	PacketVote &v = packet_vote_state();
+	const int gen = ++pc.voteGen;
+	const bool warpAll = __all_sync(SNL_FULL, pred);
+	if((threadIdx.x & 31) == 0) {
+		if(!warpAll)
+			*(volatile int *)&v.notAllGen[gen & 3] = gen;
+		__threadfence_block();
+		atomicAdd(&v.arrived, 1);
+	}
+	return gen;
+}
+__device__ __forceinline__ bool packet_vote_all(int gen) {
+	PacketVote &v = packet_vote_state();
+	const int need = gen * (int)(blockDim.x >> 5);
+	while(*(volatile int *)&v.arrived < need) {
+	}
+	__threadfence_block();
+	return *(volatile int *)&v.notAllGen[gen & 3] != gen;
+}
+
+// What one Scene::RayTrace level leaves for the final colour of a lane:
+//   out = diffuse * lDiffuse + specular * lSpecular      (src/scene_trace.cpp:504-511)
+// with diffuse possibly replaced by VLerp(transColor, diffuse, opacity) once the transparency pass behind the hit has
+// returned (:468-483).
+struct LevelOut {
+	float ar, ag, ab;  // samples.diffuse after the reflection blend
+	float lr, lg, lb;  // lDiffuse
+	float sr, sg, sb;  // specular * lSpecular
+	float opacity;
+};
+
+__device__ __forceinline__ void level_compose(const SceneDev &S, const LevelOut &f, float dr, float dg, float db, float &outr,
+											  float &outg, float &outb) {
+	if(S.nLights) {
+		outr = dr * f.lr + f.sr;
+		outg = dg * f.lg + f.sg;
+		outb = db * f.lb + f.sb;
+	}
+	else {
+		outr = dr;
+		outg = dg;
+		outb = db;
+	}
+}
+
+enum { kMaxTransp = 8 };  // transparent surfaces followed along one ray (the reference recursion has no cap)
+
+template <int LEVEL, bool SHARED, bool TRANSP>
+__device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet originPre, bool active, int maskGen,
+											  float ox, float oy, float oz, float dx, float dy, float dz, float &outr,
+											  float &outg, float &outb, PacketCounts &pc, TravCount &tc);
+
+// One level of Scene::RayTrace for the calling lane (src/scene_trace.cpp:92-520) up to, not including, the
+// transparency pass: nearest hit, Sample + material, reflection bounce (LEVEL 0), lights. Returns true when the lane
+// is in transSel with opacity < 1 (:468-472); `hitDist` is its tDistance. DEPTH0: the rays are the level's own
+// (else: a transparency continuation, counted as such). All 256 threads of the CTA must call it.
+template <int LEVEL, bool SHARED, bool TRANSP, bool DEPTH0>
+__device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet originPre, bool active, int maskGen,
+											   float ox, float oy, float oz, float dx, float dy, float dz, LevelOut &f,
+											   float &hitDist, bool &depthOnly, PacketCounts &pc, TravCount &tc) {
 	Hit h;
 	h.dist = CUDART_INF_F;
 	h.obj = 0;
@@ -613,43 +724,52 @@ __device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet or
 			traverse_nearest<true>(originPre.nodes, originPre.tris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
 		else
 			traverse_nearest<false>(S.nodes, S.gtris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
-		if(LEVEL == 0)
+		if(!DEPTH0)
+			pc.transparency++;
+		else if(LEVEL == 0)
 			pc.primary++;
 		else
 			pc.reflection++;
 	}
 	__syncwarp();
+	hitDist = h.dist;
+	f.opacity = 1.0f;
+	f.lr = f.lg = f.lb = f.sr = f.sg = f.sb = 0.0f;
 
+	depthOnly = S.gvDepth != 0;
 	if(S.gvDepth) {  // src/scene_trace.cpp:128-137
 		const float dist = active ? (h.dist > CUDART_INF_F ? 0.0f : 1.0f / h.dist) : 0.0f;
-		outr = dist * 20.0f;
-		outg = dist * 250.0f;
-		outb = dist * 2.0f;
-		return;
+		f.ar = dist * 20.0f;
+		f.ag = dist * 250.0f;
+		f.ab = dist * 2.0f;
+		return false;
 	}
 
 	const bool sel = active && h.dist < CUDART_INF_F;
 	Sample s;
-	shade_block(S, sel, h, ox, oy, oz, dx, dy, dz, packetHasMask, s);
+	bool trans;
+	// maskGen > 0: "ask packet vote maskGen" (posted by the level above before this level's traversal)
+	const bool packetHasMask = maskGen > 0 ? !packet_vote_all(maskGen) : maskGen != 0;
+	shade_block<TRANSP>(S, sel, h, ox, oy, oz, dx, dy, dz, packetHasMask, s, trans);
 
 	if(LEVEL == 0 && S.gvRefl) {  // src/scene_trace.cpp:454-466, TraceReflection :603-618
 		// selector.All() of the packet (src/scene_trace.cpp:615-617) picks RayGroup<0,0> or <0,1> for the bounce; only
-		// UberMaterial::Shade_ looks at it, so the CTA-wide vote is skipped for scenes without one
-#ifdef SNL_EXPERIMENT_NOBAR
-		const bool all = true;
-#else
-		const bool all = S.hasUber ? (bool)__syncthreads_and(sel) : true;
-#endif
+		// UberMaterial::Shade_ looks at it, so the vote is skipped for scenes without one
+		const int refMask = S.hasUber ? packet_vote_post(sel, pc) : 0;
 		float rx, ry, rz, rox, roy, roz;
 		reflection_ray(s, dx, dy, dz, rx, ry, rz, rox, roy, roz);
 		float cr = 0.0f, cg = 0.0f, cb = 0.0f;
-		raytrace_lane<1, false>(S, PreSet{nullptr, nullptr}, sel, !all, rox, roy, roz, rx, ry, rz, cr, cg, cb, pc, tc);
+		raytrace_lane<1, false, TRANSP>(S, PreSet{nullptr, nullptr}, sel, refMask, rox, roy, roz, rx, ry, rz, cr, cg, cb, pc, tc);
 		if(sel) {
 			s.dr = s.dr + (cr - s.dr) * 0.3f;
 			s.dg = s.dg + (cg - s.dg) * 0.3f;
 			s.db = s.db + (cb - s.db) * 0.3f;
 		}
 	}
+	f.ar = s.dr;
+	f.ag = s.dg;
+	f.ab = s.db;
+	f.opacity = s.opacity;
 
 	if(S.nLights) {
 		float ldr = S.ambient[0], ldg = S.ambient[1], ldb = S.ambient[2];
@@ -664,26 +784,87 @@ __device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet or
 			}
 			__syncwarp();
 		}
-		outr = s.dr * ldr + s.sr * lsr;
-		outg = s.dg * ldg + s.sg * lsg;
-		outb = s.db * ldb + s.sb * lsb;
+		f.lr = ldr;
+		f.lg = ldg;
+		f.lb = ldb;
+		f.sr = s.sr * lsr;
+		f.sg = s.sg * lsg;
+		f.sb = s.sb * lsb;
 	}
-	else {
-		outr = s.dr;
-		outg = s.dg;
-		outb = s.db;
+	return TRANSP && trans && s.opacity < 1.0f;
+}
+
+// Scene::RayTrace for the calling lane. LEVEL 0 = the caller's rays, LEVEL 1 = the reflection pass
+// (cache.reflections == 1: no further bounce). TRANSP adds the transparency pass (TraceTransparency,
+// src/scene_trace.cpp:468-483,620-634): the reference recurses with the transSel lanes continued from
+// dir * (t + 0.001) + origin and lerps the result into diffuse BEFORE the lights are applied; lights and the bounce do
+// not depend on that result, so the recursion is unrolled into a loop that keeps one LevelOut per surface and composes
+// the colours back to front afterwards with the reference's expression order. All 256 threads must call it.
+template <int LEVEL, bool SHARED, bool TRANSP>
+__device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet originPre, bool active, int maskGen,
+											  float ox, float oy, float oz, float dx, float dy, float dz, float &outr,
+											  float &outg, float &outb, PacketCounts &pc, TravCount &tc) {
+	LevelOut f;
+	float hitDist;
+	bool depthOnly;
+	bool cont = raytrace_level<LEVEL, SHARED, TRANSP, true>(S, originPre, active, maskGen, ox, oy, oz, dx, dy, dz, f,
+															hitDist, depthOnly, pc, tc);
+	if(depthOnly) {
+		outr = f.ar;
+		outg = f.ag;
+		outb = f.ab;
+		return;
 	}
+	if(TRANSP) {
+		LevelOut behind[kMaxTransp];
+		int depth = 0;
+		for(;;) {
+			cont = cont && depth < kMaxTransp;
+			// transSel.Any() / transSel.All() of the packet (src/scene_trace.cpp:474, :630-633)
+			const int n = __syncthreads_count(cont);
+			if(n == 0)
+				break;
+			if(cont) {
+				behind[depth++] = f;
+				const float t = hitDist + 0.001f;
+				ox = dx * t + ox;
+				oy = dy * t + oy;
+				oz = dz * t + oz;
+			}
+			// every lane takes part (shading blocks are warp-wide); only continued lanes take the new level's result
+			LevelOut nf;
+			float nDist;
+			const bool more = raytrace_level<LEVEL, false, TRANSP, false>(S, PreSet{nullptr, nullptr}, cont, n != kPacket ? -1 : 0, ox,
+																		  oy, oz, dx, dy, dz, nf, nDist, depthOnly, pc, tc);
+			if(cont) {
+				f = nf;
+				hitDist = nDist;
+			}
+			cont = cont && more;
+		}
+		level_compose(S, f, f.ar, f.ag, f.ab, outr, outg, outb);
+		while(depth > 0) {
+			const LevelOut &b = behind[--depth];
+			// VLerp(transColor, diffuse, opacity) = transColor + (diffuse - transColor) * opacity
+			const float r = outr + (b.ar - outr) * b.opacity;
+			const float g = outg + (b.ag - outg) * b.opacity;
+			const float bl = outb + (b.ab - outb) * b.opacity;
+			level_compose(S, b, r, g, bl, outr, outg, outb);
+		}
+	}
+	else
+		level_compose(S, f, f.ar, f.ag, f.ab, outr, outg, outb);
 }
 
 // CTA-level aggregation of the per-lane ray counters into the scene's global counters.
 __device__ __forceinline__ void flush_counts(const SceneDev &S, const PacketCounts &pc, const TravCount &tc) {
-	__shared__ unsigned sh[7];
-	if(threadIdx.x < 7)
+	__shared__ unsigned sh[8];
+	if(threadIdx.x < 8)
 		sh[threadIdx.x] = 0;
 	__syncthreads();
-	unsigned v[7] = {pc.primary, pc.shadow, pc.reflection, pc.reflection_shadow, tc.nodes, tc.tris, tc.gtris};
+	unsigned v[8] = {pc.primary, pc.shadow, pc.reflection, pc.reflection_shadow, tc.nodes, tc.tris, tc.gtris, pc.transparency};
 #pragma unroll
-	for(int i = 0; i < 7; i++) {
+	for(int i = 0; i < 8; i++) {
 		unsigned x = v[i];
 #pragma unroll
 		for(int o = 16; o; o >>= 1)
@@ -692,7 +873,7 @@ __device__ __forceinline__ void flush_counts(const SceneDev &S, const PacketCoun
 			atomicAdd(&sh[i], x);
 	}
 	__syncthreads();
-	if(threadIdx.x < 7 && sh[threadIdx.x])
+	if(threadIdx.x < 8 && sh[threadIdx.x])
 		atomicAdd(reinterpret_cast<unsigned long long *>(S.counters) + threadIdx.x, (unsigned long long)sh[threadIdx.x]);
 }
 

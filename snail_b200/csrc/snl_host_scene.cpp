@@ -970,12 +970,13 @@ bool load_obj_scene(const char *objPath, const char *mtlPath, const char *texDir
 		HostMaterial hm;
 		hm.name = d.name;
 		memset(&hm.m, 0, sizeof(hm.m));
-		hm.m.texture = -1;
+		hm.m.texture = hm.m.mask_texture = -1;
 		const bool diff = texIndex.count(d.diffuseMap) != 0, trans = texIndex.count(d.dissolveMap) != 0;
 		if(diff && trans) {
 			hm.m.kind = SNL_MAT_TRANSPARENT;
 			hm.m.flags = SNL_MATF_TEXCOORDS | SNL_MATF_TRANSPARENCY;
 			hm.m.texture = texIndex[d.diffuseMap];
+			hm.m.mask_texture = texIndex[d.dissolveMap];
 		}
 		else if(diff) {
 			hm.m.kind = SNL_MAT_TEX;

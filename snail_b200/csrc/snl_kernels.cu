@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(kPacket) k_primary(SceneDev S, const PreSet pr
 	const int px0 = (blockIdx.x % packetsX) * 16, py0 = (blockIdx.x / packetsX) * 16;
 	const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
 	const int x = px0 + tx, y = py0 + ty;
-	PacketCounts pc = {0, 0, 0, 0};
+	PacketCounts pc = {0, 0, 0, 0, 0};
 	TravCount tc = {0, 0, 0};
 	const bool inside = x < W && y < H;
 	if(inside) {
@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(kPacket) k_trace_rays(SceneDev S, const PreSet
 													 int n, int *__restrict__ triId, float *__restrict__ t,
 													 float *__restrict__ bary) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
-	PacketCounts pc = {0, 0, 0, 0};
+	PacketCounts pc = {0, 0, 0, 0, 0};
 	TravCount tc = {0, 0, 0};
 	if(i < n) {
 		const bool active = !mask || mask[i];
@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(kPacket) k_trace_rays(SceneDev S, const PreSet
 __global__ void __launch_bounds__(kPacket) k_trace_shadow(SceneDev S, const PreSet pre, float ox, float oy, float oz,
 													   const float *__restrict__ d3, float *__restrict__ tmax, int n) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
-	PacketCounts pc = {0, 0, 0, 0};
+	PacketCounts pc = {0, 0, 0, 0, 0};
 	TravCount tc = {0, 0, 0};
 	if(i < n) {
 		const float dist = tmax[i];
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(kPacket) k_trace_shadow(SceneDev S, const PreS
 }
 
 // ---- Scene::RayTrace on caller rays, 256-ray packets (snl_raytrace) -----------------------------------------
-template <bool SHARED>
+template <bool SHARED, bool TRANSP>
 __global__ void __launch_bounds__(kPacket) k_raytrace(SceneDev S, const PreSet pre, const float *__restrict__ o3,
 												   const float *__restrict__ d3, const unsigned char *__restrict__ mask,
 												   int n, float *__restrict__ rgb3) {
@@ -149,10 +149,11 @@ __global__ void __launch_bounds__(kPacket) k_raytrace(SceneDev S, const PreSet p
 	const float ox = o[0], oy = o[1], oz = o[2];
 	const float dx = d3[(size_t)src * 3 + 0], dy = d3[(size_t)src * 3 + 1], dz = d3[(size_t)src * 3 + 2];
 	const bool all = __syncthreads_and(active);
-	PacketCounts pc = {0, 0, 0, 0};
+	packet_vote_init();
+	PacketCounts pc = {0, 0, 0, 0, 0};
 	TravCount tc = {0, 0, 0};
 	float r = 0.0f, g = 0.0f, b = 0.0f;
-	raytrace_lane<0, SHARED>(S, pre, active, !SHARED && !all, ox, oy, oz, dx, dy, dz, r, g, b, pc, tc);
+	raytrace_lane<0, SHARED, TRANSP>(S, pre, active, (!SHARED && !all) ? -1 : 0, ox, oy, oz, dx, dy, dz, r, g, b, pc, tc);
 	if(i < n) {
 		rgb3[(size_t)i * 3 + 0] = r;
 		rgb3[(size_t)i * 3 + 1] = g;
@@ -175,6 +176,9 @@ __device__ __forceinline__ unsigned conv_channel(float c) {
 #ifndef SNL_RENDER_MIN_BLOCKS
 #define SNL_RENDER_MIN_BLOCKS 4
 #endif
+// TRANSP: the scene has a material that can start a transparency pass. SUPER: gVals[9], every 16x16 output packet is
+// traced as four 16x16 packets of the 2W x 2H image and box-filtered (src/render.cpp:71-110).
+template <bool TRANSP, bool SUPER>
 __global__ void __launch_bounds__(kPacket, SNL_RENDER_MIN_BLOCKS) k_render(SceneDev S, const PreSet pre, RayGenParams g, int W, int H,
 												 int packetsX, const int4 *__restrict__ packets,
 												 unsigned char *__restrict__ out, size_t pitch) {
@@ -193,28 +197,50 @@ __global__ void __launch_bounds__(kPacket, SNL_RENDER_MIN_BLOCKS) k_render(Scene
 		ch = min(16, H - py0);
 	}
 	const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-	float dx, dy, dz;
-	gen_primary(g, px0, py0, tx, ty, dx, dy, dz);
-	PacketCounts pc = {0, 0, 0, 0};
+	PacketCounts pc = {0, 0, 0, 0, 0};
 	TravCount tc = {0, 0, 0};
-	float r = 0.0f, gg = 0.0f, b = 0.0f;
+	if(S.hasUber)
+		packet_vote_init();
 	// Like the reference we trace the whole 16x16 packet even when it overhangs the image or the tile
 	// (src/render.cpp:112-115): overhanging lanes take part in the 16-lane shading blocks and in the packet-wide
 	// selector.All() test of the reflection pass (src/scene_trace.cpp:615-617), and TreeStats counts them.
 	const bool active = true;
-	raytrace_lane<0, true>(S, pre, active, false, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, r, gg, b, pc, tc);
-	if(S.gvTint) {  // src/render.cpp:118-132
-		r = (r + 0.1f) * S.tint[0];
-		gg = (gg + 0.1f) * S.tint[1];
-		b = (b + 0.1f) * S.tint[2];
+	for(int k = 0; k < (SUPER ? 4 : 1); k++) {
+		float dx, dy, dz;
+		if(SUPER)  // offx / offy of src/render.cpp:72
+			gen_primary(g, px0 * 2 + (k & 1) * 16, py0 * 2 + (k >> 1) * 16, tx, ty, dx, dy, dz);
+		else
+			gen_primary(g, px0, py0, tx, ty, dx, dy, dz);
+		float r = 0.0f, gg = 0.0f, b = 0.0f;
+		raytrace_lane<0, true, TRANSP>(S, pre, active, 0, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, r, gg, b, pc, tc);
+		int ox = tx, oy = ty;
+		bool store = true;
+		if(SUPER) {
+			// (tcolors[q] + tcolors[q + line]) * 0.25: rows 2j and 2j+1 of the packet are lanes l and l+16 of one warp;
+			// then col[0] + col[1] / col[2] + col[3]: even + odd pixel (src/render.cpp:92-101)
+			r = (r + __shfl_down_sync(SNL_FULL, r, 16)) * 0.25f;
+			gg = (gg + __shfl_down_sync(SNL_FULL, gg, 16)) * 0.25f;
+			b = (b + __shfl_down_sync(SNL_FULL, b, 16)) * 0.25f;
+			r = r + __shfl_down_sync(SNL_FULL, r, 1);
+			gg = gg + __shfl_down_sync(SNL_FULL, gg, 1);
+			b = b + __shfl_down_sync(SNL_FULL, b, 1);
+			store = !(ty & 1) && !(tx & 1);
+			ox = (k & 1) * 8 + (tx >> 1);
+			oy = (k >> 1) * 8 + (ty >> 1);
+		}
+		if(S.gvTint) {  // src/render.cpp:118-132
+			r = (r + 0.1f) * S.tint[0];
+			gg = (gg + 0.1f) * S.tint[1];
+			b = (b + 0.1f) * S.tint[2];
+		}
+		if(store && ox < cw && oy < ch) {
+			unsigned char *dst = out + (size_t)(py0 + oy) * pitch + (size_t)(px0 + ox) * 3;
+			dst[0] = (unsigned char)conv_channel(b);
+			dst[1] = (unsigned char)conv_channel(gg);
+			dst[2] = (unsigned char)conv_channel(r);
+		}
+		__syncwarp();
 	}
-	if(tx < cw && ty < ch) {
-		unsigned char *dst = out + (size_t)(py0 + ty) * pitch + (size_t)(px0 + tx) * 3;
-		dst[0] = (unsigned char)conv_channel(b);
-		dst[1] = (unsigned char)conv_channel(gg);
-		dst[2] = (unsigned char)conv_channel(r);
-	}
-	__syncwarp();
 	flush_counts(S, pc, tc);
 }
 
@@ -262,10 +288,17 @@ cudaError_t launch_raytrace(const SceneDev &S, const PreSet &pre, const float *o
 							const unsigned char *mask, int n, bool shared, float *rgb3, cudaStream_t st) {
 	if(n <= 0)
 		return cudaSuccess;
-	if(shared)
-		k_raytrace<true><<<blocks_for(n, kPacket), kPacket, 0, st>>>(S, pre, o3, d3, mask, n, rgb3);
+	const unsigned grid = blocks_for(n, kPacket);
+	if(S.hasTransp) {
+		if(shared)
+			k_raytrace<true, true><<<grid, kPacket, 0, st>>>(S, pre, o3, d3, mask, n, rgb3);
+		else
+			k_raytrace<false, true><<<grid, kPacket, 0, st>>>(S, pre, o3, d3, mask, n, rgb3);
+	}
+	else if(shared)
+		k_raytrace<true, false><<<grid, kPacket, 0, st>>>(S, pre, o3, d3, mask, n, rgb3);
 	else
-		k_raytrace<false><<<blocks_for(n, kPacket), kPacket, 0, st>>>(S, pre, o3, d3, mask, n, rgb3);
+		k_raytrace<false, false><<<grid, kPacket, 0, st>>>(S, pre, o3, d3, mask, n, rgb3);
 	return cudaGetLastError();
 }
 
@@ -275,7 +308,16 @@ cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenPara
 	const int grid = packets ? nPackets : px * py;
 	if(grid <= 0)
 		return cudaSuccess;
-	k_render<<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+	if(S.hasTransp) {
+		if(S.gvSuper)
+			k_render<true, true><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+		else
+			k_render<true, false><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+	}
+	else if(S.gvSuper)
+		k_render<false, true><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+	else
+		k_render<false, false><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
 	return cudaGetLastError();
 }
 

@@ -70,7 +70,7 @@ struct snl_scene {
 	snl::DevBuf<int> dTriMat;
 	int nTriMat = 0;
 	snl::DevBuf<snl::DevMaterial> dMats;
-	int nMats = 0, hasUber = 0;
+	int nMats = 0, hasUber = 0, hasTransp = 0;
 	snl::DevBuf<snl::DevTexture> dTexs;
 	std::vector<snl::DevBuf<unsigned char>> dTexData;
 

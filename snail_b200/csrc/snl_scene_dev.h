@@ -26,6 +26,8 @@ struct SceneDev {
 	int nTriMat, nMats, nLights;
 	float ambient[3];
 	int gvDepth, gvFull, gvRefl, gvTint;  // gVals[1], [6], [7], [8]
+	int gvSuper;                          // gVals[9]: 2x2 supersampling in Render()
+	int hasTransp;                        // a material can start a transparency pass (fTransparency and opacity < 1)
 	int hasUber;                          // any UberMaterial in the table (its Shade depends on the packet mask)
 	float tint[3];
 	Counters *counters;

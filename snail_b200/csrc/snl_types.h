@@ -89,6 +89,7 @@ struct DevMaterial {
 	float specular[3];
 	float opacity;
 	int32_t texture;
+	int32_t texture2;  // TransparentMaterial: the opacity (map_d) texture
 };
 
 enum { kMaxMips = 16 };  // PointSampler::mipPitch[16], src/sampling/point_sampler.h:28
@@ -114,7 +115,7 @@ struct RayGenParams {
 };
 
 struct Counters {
-	unsigned long long primary, shadow, reflection, reflection_shadow, node_visits, tri_tests, gtri_tests;
+	unsigned long long primary, shadow, reflection, reflection_shadow, node_visits, tri_tests, gtri_tests, transparency;
 };
 
 }  // namespace snl

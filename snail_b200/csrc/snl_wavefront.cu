@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(kPacket) k_wf_primary(SceneDev S, const PreSet
 	const unsigned id = blockIdx.x * kPacket + threadIdx.x;
 	float dx, dy, dz;
 	gen_primary(g, px0, py0, tx, ty, dx, dy, dz);
-	PacketCounts pc = {0, 0, 0, 0};
+	PacketCounts pc = {0, 0, 0, 0, 0};
 	TravCount tc = {0, 0, 0};
 
 	Hit h;
@@ -89,7 +89,8 @@ __global__ void __launch_bounds__(kPacket) k_wf_primary(SceneDev S, const PreSet
 	__syncwarp();
 	const bool sel = h.dist < CUDART_INF_F;
 	Sample s;
-	shade_block(S, sel, h, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, false, s);
+	bool trans;  // transparency and supersampling frames always take the fused kernel
+	shade_block<false>(S, sel, h, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, false, s, trans);
 
 	// the bounce: ray + queue entry (traced by k_wf_trace<0>)
 	float rx, ry, rz, rox, roy, roz;
@@ -266,7 +267,7 @@ __global__ void __launch_bounds__(256, SNL_WF_MIN_BLOCKS) k_wf_trace(SceneDev S,
 			idle = true;
 		}
 	}
-	PacketCounts pc = {0, 0, 0, 0};
+	PacketCounts pc = {0, 0, 0, 0, 0};
 	__syncwarp();
 	flush_counts(S, pc, tc);
 }
@@ -276,7 +277,7 @@ __global__ void __launch_bounds__(kPacket) k_wf_shade(SceneDev S, WfBuffers B) {
 	const unsigned id = blockIdx.x * kPacket + threadIdx.x;
 	const float4 o = ld4(B.rayO + id), d = ld4(B.rayD + id);
 	const bool active = o.w != 0.0f;  // sel of level 0
-	PacketCounts pc = {0, 0, 0, 0};
+	PacketCounts pc = {0, 0, 0, 0, 0};
 	TravCount tc = {0, 0, 0};
 	Hit h;
 	h.dist = CUDART_INF_F;
@@ -293,7 +294,8 @@ __global__ void __launch_bounds__(kPacket) k_wf_shade(SceneDev S, WfBuffers B) {
 	const bool all = S.hasUber ? (bool)__syncthreads_and(active) : true;
 	const bool sel = active && h.dist < CUDART_INF_F;
 	Sample s;
-	shade_block(S, sel, h, o.x, o.y, o.z, d.x, d.y, d.z, !all, s);
+	bool trans;
+	shade_block<false>(S, sel, h, o.x, o.y, o.z, d.x, d.y, d.z, !all, s, trans);
 	st4(B.st1 + 0 * B.NL + id, s.dr, s.dg, s.db, sel ? 1.0f : 0.0f);
 	st4(B.st1 + 1 * B.NL + id, s.sr, s.sg, s.sb, 0.0f);
 	B.occl[id] = 0;

@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol(sb):
     L = sb.load_library()
     for name in header_symbols():
         assert hasattr(L, name), f"{name} declared in include/snail_b200.h but not exported"
-    assert L.snl_abi_version() == 1
+    assert L.snl_abi_version() == 2
 
 
 def test_counters_build_exports_the_same_abi(sb):
@@ -37,8 +37,8 @@ def test_counters_build_exports_the_same_abi(sb):
 def test_struct_layouts_match_the_header(sb):
     assert C.sizeof(sb.Camera) == 13 * 4
     assert C.sizeof(sb.Light) == 36  # src/light.h: 9 floats
-    assert C.sizeof(sb.api.Material) == 4 * 10
-    assert C.sizeof(sb.Stats) == 8 * 8 + 8  # 8 u64 + float (padded)
+    assert C.sizeof(sb.api.Material) == 4 * 11
+    assert C.sizeof(sb.Stats) == 9 * 8 + 8  # 9 u64 + float (padded)
     assert sb.NODE_DTYPE.itemsize == 32 and sb.TRI_DTYPE.itemsize == 64 and sb.SHTRI_DTYPE.itemsize == 64
 
 

@@ -13,11 +13,14 @@ pytestmark = pytest.mark.gpu
 
 MANIFEST = json.load(open(os.path.join(GOLDEN, "manifest.json")))
 STAGES = {"simple_nolight": ({}, False), "depth": ({1: 1}, False), "simple_light": ({}, True),
-          "full_light": ({6: 1}, True), "whitted": ({6: 1, 7: 1}, True)}
+          "full_light": ({6: 1}, True), "whitted": ({6: 1, 7: 1}, True),
+          "whitted_ss": ({6: 1, 7: 1, 9: 1}, True)}
 T_REL = 1e-5
 
 
 def find(sub, name):
+    if name.startswith("@"):  # authored scene committed under data/ (tools/make_panes.py)
+        return os.path.join(DATA, name[1:])
     for d in (os.path.join(ROOT, "assets"), os.path.join(ROOT, "oracle", "_ref")):
         p = os.path.join(d, sub, name)
         if os.path.exists(p):
@@ -69,12 +72,13 @@ def test_render_stages_vs_golden(sb, name):
         sc.set_lights([light] if lit else [])
         img, st = sc.render(cam, W, H)
         err = np.abs(img.astype(np.int16) - g["img_" + stage].astype(np.int16)).max(axis=2)
+        undef = g["undef_" + stage] if stage != "depth" else g["undef_simple"]
         if stage != "depth":
-            err[g["undef_simple"]] = 0  # pixels the reference shades from uninitialised memory
+            err[undef] = 0  # pixels the reference shades from uninitialised memory
         frac = float((err <= 1).mean())
         print(f"{name}/{stage}: within 1/255 on {frac*100:.3f}% (max err {int(err.max())}), rays {st['rays']} golden {c['rays'][stage]}")
         assert frac >= 0.999, stage
-        assert abs(st["rays"] - c["rays"][stage]) <= max(int(g["undef_simple"].sum()), 0.002 * c["rays"][stage])
+        assert abs(st["rays"] - c["rays"][stage]) <= max(4 * int(undef.sum()), 0.002 * c["rays"][stage])
 
 
 @pytest.mark.parametrize("name", list(MANIFEST["cases"]))

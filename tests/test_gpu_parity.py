@@ -278,7 +278,7 @@ def test_tiles_and_device_output(sb):
 def test_unsupported_options_fail_loudly(sb):
     sc = sb.Scene(0)
     with pytest.raises(sb.SnlError):
-        sc.set_options({9: 1})
+        sc.set_options({5: 1})  # packet statistics heat-map: no per-ray equivalent
     with pytest.raises(sb.SnlError):
         sc.trace_primary(sb.Camera((0, 0, 0)), 16, 16)  # no geometry yet
 

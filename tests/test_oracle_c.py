@@ -11,10 +11,13 @@ from conftest import DATA, GOLDEN, ROOT
 
 MANIFEST = json.load(open(os.path.join(GOLDEN, "manifest.json")))
 STAGES = {"simple_nolight": ({}, False), "depth": ({1: 1}, False), "simple_light": ({}, True),
-          "full_light": ({6: 1}, True), "whitted": ({6: 1, 7: 1}, True)}
+          "full_light": ({6: 1}, True), "whitted": ({6: 1, 7: 1}, True),
+          "whitted_ss": ({6: 1, 7: 1, 9: 1}, True)}
 
 
 def find(sub, name):
+    if name.startswith("@"):  # authored scene committed under data/ (tools/make_panes.py)
+        return os.path.join(DATA, name[1:])
     for d in (os.path.join(ROOT, "assets"), os.path.join(ROOT, "oracle", "_ref")):
         p = os.path.join(d, sub, name)
         if os.path.exists(p):
@@ -68,9 +71,10 @@ def test_c_oracle_frames_vs_golden(sb, name):
         orc.set_lights([g["light"]] if lit else [])
         img, st = orc.render(g["camera"], W, H)
         err = np.abs(img.astype(np.int16) - g["img_" + stage].astype(np.int16)).max(axis=2)
+        undef = g["undef_" + stage] if stage != "depth" else g["undef_simple"]
         if stage != "depth":
-            err[g["undef_simple"]] = 0
+            err[undef] = 0
         frac = float((err <= 1).mean())
         assert frac >= 0.999, (stage, frac)
-        assert abs(st["rays"] - c["rays"][stage]) <= max(int(g["undef_simple"].sum()), 0.002 * c["rays"][stage]), stage
+        assert abs(st["rays"] - c["rays"][stage]) <= max(4 * int(undef.sum()), 0.002 * c["rays"][stage]), stage
     orc.close()

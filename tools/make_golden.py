@@ -25,6 +25,9 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
 import snailref as R  # noqa: E402
+import snail_oracle as O  # noqa: E402
+sys.path.insert(0, ROOT)
+import snail_b200 as sb  # noqa: E402  (host ingest + builder only: no device needed)
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 SCENES = os.path.join(ROOT, "oracle", "_ref", "scenes")
@@ -37,6 +40,7 @@ STAGES = {
     "simple_light": ({}, True),
     "full_light": ({6: 1}, True),
     "whitted": ({6: 1, 7: 1}, True),
+    "whitted_ss": ({6: 1, 7: 1, 9: 1}, True),  # + 2x2 supersampling (src/render.cpp:71-110)
 }
 
 # name -> (obj, mtl, inside camera, W, H)
@@ -45,7 +49,11 @@ CASES = {
     "lancia": ("lancia.obj", None, False, 128, 80),
     "feline": ("feline.obj", None, False, 128, 80),
     "barracks_tex": ("barracks.obj", "barracks.mtl", False, 128, 80),
+    # authored multi-material scene (tools/make_panes.py): Uber d < 1, TransparentMaterial, transparency chains
+    "panes": ("@panes.obj", "panes.mtl", False, 128, 80),
 }
+# cases with a fixed camera / light instead of bench_camera: name -> (camera pos, light [pos, color, radius])
+VIEWS = {"panes": ((0.0, 0.0, -2.0), [0.5, 1.0, -2.0, 1.0, 1.0, 1.0, 12.0])}
 
 
 def random_rays(n, bmin, bmax, seed):
@@ -69,9 +77,13 @@ def main():
                 "backend": R.lib("scalar").ref_backend().decode(), "cases": {}}
     for name, (obj, mtl, inside, W, H) in CASES.items():
         mtl_path = os.path.join(DATA, mtl) if mtl else None
-        ref = R.RefScene(os.path.join(SCENES, obj), mtl_path, TEXDIR if mtl else "", variant="scalar")
+        obj_path = os.path.join(DATA, obj[1:]) if obj.startswith("@") else os.path.join(SCENES, obj)
+        ref = R.RefScene(obj_path, mtl_path, TEXDIR if mtl else "", variant="scalar")
         bmin, bmax = ref.bbox()
         cam, light = R.bench_camera(bmin, bmax, inside=inside)
+        if name in VIEWS:
+            cam = R.camera_array(VIEWS[name][0])
+            light = np.array(VIEWS[name][1], np.float32)
         out = {"camera": cam, "light": light, "size": np.array([W, H], np.int32)}
         ref.set_gvals({})
         ref.set_lights([])
@@ -84,6 +96,17 @@ def main():
         # stack held. Those pixels are undefined behaviour in the reference and are excluded from image goldens.
         lane0 = np.repeat(tri[:, 0::4], 4, axis=1)[:, :W]
         out["undef_simple"] = (tri == 0) & (lane0 < 0)
+        # the same on the 2W x 2H grid the supersampled frame is traced on, reduced to output pixels
+        tri2, _, _ = ref.trace_primary(cam, 2 * W, 2 * H)
+        lane02 = np.repeat(tri2[:, 0::4], 4, axis=1)[:, :2 * W]
+        u2 = (tri2 == 0) & (lane02 < 0)
+        out["undef_ss"] = u2.reshape(H, 2, W, 2).any(axis=(1, 3))
+        # The same quirk at the deeper levels (reflection / transparency packets are masked, and a masked lane 0 reads
+        # object 0 as well): which pixels it reaches is worked out by the plain-C restatement, which follows the
+        # reference's packet / quad structure and flags those lanes (oracle/snail_oracle.c shade_block).
+        hs = sb.HostScene(obj_path, mtl_path, TEXDIR if mtl else "")
+        hn, ht, hsh, hm = hs.bvh()
+        orc = O.OracleScene(hn, ht, hsh, hm, hs.materials(), hs.textures())
         rays = {}
         for stage, (gv, lit) in STAGES.items():
             ref.set_gvals(gv)
@@ -91,6 +114,13 @@ def main():
             img, st, _ = ref.render(cam, W, H, threads=1)
             out["img_" + stage] = img
             rays[stage] = st["rays"]
+            if stage != "depth":
+                orc.set_gvals(gv)
+                orc.set_lights([light] if lit else [])
+                u = np.zeros((H, W), np.uint8)
+                orc.render(cam, W, H, undef=u)
+                out["undef_" + stage] = (u != 0) | (out["undef_ss"] if stage.endswith("_ss") else out["undef_simple"])
+        orc.close()
         # incoherent rays with their own origins (Context<0,0> / <0,1>)
         n = 256 * 3 + 77
         o, d = random_rays(n, bmin, bmax, 7)
