@@ -42,17 +42,32 @@ struct TravCount {
 	unsigned nodes, tris, gtris;  // inner nodes fetched, PreTri records tested, GenTri records tested
 };
 
-// BBox::Test, one ray vs one box (src/bounding_box.cpp:61-97): hit <=> lmax >= 0 && lmin <= min(lmax, dist).
-__device__ __forceinline__ bool box_test(float minx, float maxx, float miny, float maxy, float minz, float maxz, float ox,
-										 float oy, float oz, float ix, float iy, float iz, float dist, float &lminOut) {
-	float l1 = ix * (minx - ox), l2 = ix * (maxx - ox);
+// BBox::Test, one ray vs one box (src/bounding_box.cpp:61-97): hit <=> lmax >= 0 && lmin <= min(lmax, dist), for a ray
+// with its own origin. The reference evaluates idir * (plane - origin); here each plane costs ONE fused multiply-add
+// plane * idir - origin * idir (oi* = origin * idir, once per ray). The slab distances differ from the reference's by
+// an ulp or two, which can only flip the verdict for a ray grazing the box surface; which triangle is hit, and t / u /
+// v, come from the triangle test alone and stay bit-identical (tests/test_gpu_golden.py).
+__device__ __forceinline__ bool box_test(float minx, float maxx, float miny, float maxy, float minz, float maxz, float oix,
+										 float oiy, float oiz, float ix, float iy, float iz, float dist, float &lminOut) {
+#ifndef SNL_BOX_EXACT
+	float l1 = fmaf(minx, ix, -oix), l2 = fmaf(maxx, ix, -oix);
 	float lmin = fminf(l1, l2), lmax = fmaxf(l1, l2);
-	l1 = iy * (miny - oy);
-	l2 = iy * (maxy - oy);
+	l1 = fmaf(miny, iy, -oiy);
+	l2 = fmaf(maxy, iy, -oiy);
 	lmin = fmaxf(lmin, fminf(l1, l2));
 	lmax = fminf(lmax, fmaxf(l1, l2));
-	l1 = iz * (minz - oz);
-	l2 = iz * (maxz - oz);
+	l1 = fmaf(minz, iz, -oiz);
+	l2 = fmaf(maxz, iz, -oiz);
+#else  // oi* = the origin itself: the reference's expression
+	float l1 = ix * (minx - oix), l2 = ix * (maxx - oix);
+	float lmin = fminf(l1, l2), lmax = fmaxf(l1, l2);
+	l1 = iy * (miny - oiy);
+	l2 = iy * (maxy - oiy);
+	lmin = fmaxf(lmin, fminf(l1, l2));
+	lmax = fminf(lmax, fmaxf(l1, l2));
+	l1 = iz * (minz - oiz);
+	l2 = iz * (maxz - oiz);
+#endif
 	lmin = fmaxf(lmin, fminf(l1, l2));
 	lmax = fminf(lmax, fmaxf(l1, l2));
 	lminOut = lmin;
@@ -234,6 +249,11 @@ __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nod
 	// memory; stack[-1] is a guard slot because popping the sentinel reads it
 	SNL_STACK_DECL();
 	int cur = 0;
+#ifndef SNL_BOX_EXACT
+	const float bx = ox * ix, by = oy * iy, bz = oz * iz;  // box_test's origin * idir
+#else
+	const float bx = ox, by = oy, bz = oz;
+#endif
 	while(cur != kSentinel) {
 		int leaf = 0;  // parked leaf link (< 0), 0 = none
 		while((unsigned)cur < (unsigned)kSentinel) {
@@ -241,7 +261,7 @@ __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nod
 			bool h0, h1;
 			float lmin0, lmin1;
 			int l0, l1;
-			node_test<SHARED>(nodes + cur, ox, oy, oz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
+			node_test<SHARED>(nodes + cur, bx, by, bz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
 			SNL_TRAVERSE_STEP();
 			if(!__any_sync(__activemask(), leaf == 0))
 				break;

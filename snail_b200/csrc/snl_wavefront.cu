@@ -223,7 +223,11 @@ __global__ void __launch_bounds__(256, SNL_WF_MIN_BLOCKS) k_wf_trace(SceneDev S,
 			bool h0, h1;
 			float lmin0, lmin1;
 			int l0, l1;
+#ifndef SNL_BOX_EXACT  // box_test takes origin * idir (loop-invariant: hoisted out of the walk)
+			node_test<SHADOW>(nodes + cur, ox * ix, oy * iy, oz * iz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
+#else
 			node_test<SHADOW>(nodes + cur, ox, oy, oz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
+#endif
 			SNL_TRAVERSE_STEP();
 			if(!__any_sync(__activemask(), leaf == 0))
 				break;

@@ -53,7 +53,8 @@ CASES = {
     "panes": ("@panes.obj", "panes.mtl", False, 128, 80),
 }
 # cases with a fixed camera / light instead of bench_camera: name -> (camera pos, light [pos, color, radius])
-VIEWS = {"panes": ((0.0, 0.0, -2.0), [0.5, 1.0, -2.0, 1.0, 1.0, 1.0, 12.0])}
+# (camera slightly off the axes of symmetry: with it at x = y = 0 reflected rays run exactly into the room's corner edges)
+VIEWS = {"panes": ((0.0137, 0.0211, -2.0), [0.5, 1.0, -2.0, 1.0, 1.0, 1.0, 12.0])}
 
 
 def random_rays(n, bmin, bmax, seed):
