@@ -111,6 +111,15 @@ void snl_scene_destroy(snl_scene *);
 int snl_scene_set_geometry(snl_scene *, const void *nodes, int nNodes, const void *tris, const void *shTris,
 						   int nTris, const int *triMatId, int nMatIds);
 
+/* Device-side replacement of BVH::Construct (src/bvh/tree.cpp:289-328) for a triangle soup: tris / shTris (may be
+ * NULL) / triMatId as in snl_scene_set_geometry, in any order. Builds a Morton-order linear BVH on the GPU (radix
+ * sort + Karras hierarchy + bottom-up refit with SAH leaf collapse, snail_b200/csrc/snl_build.cu) straight into the
+ * traversal layout. NOT the reference's tree: hits are identical wherever they are unambiguous, triangle ids refer
+ * to the builder's own order (use t / barycentrics / frames to compare). snl_scene_build_ms = device time of it. */
+int snl_scene_build_device(snl_scene *, const void *tris, const void *shTris, int nTris, const int *triMatId,
+						   int nMatIds);
+float snl_scene_build_ms(snl_scene *);
+
 /* Scene::materials / texDict (src/scene.h:25-40, src/scene.cpp:12-21). */
 int snl_scene_set_materials(snl_scene *, const snl_material *mats, int nMats, const snl_texture *tex, int nTex);
 
@@ -127,7 +136,9 @@ int snl_set_options(snl_scene *, const int gVals[16]);
  * BVH::Construct (src/bvh/tree.cpp:293-328), LoadMaterialDescs/LoadTextures/MakeMaterials
  * (src/shading/material.cpp:59-192), exactly the set-up of src/rtracer.cpp:505-586; then the flatten step.
  * flipNormalsFlag / buildFlags as conf.flipNormals / conf.buildFlags there (flag 0 => normals ARE flipped;
- * buildFlags: 1 noShadingData, 2 fastBuild, 4 useSah). mtlPath/texDir may be NULL. */
+ * buildFlags: 1 noShadingData, 2 fastBuild, 4 useSah; ours: 8 = SNL_BUILD_DEVICE, the host only parses the file and
+ * the tree is built on the GPU, see snl_scene_build_device). mtlPath/texDir may be NULL. */
+#define SNL_BUILD_DEVICE 8
 int snl_scene_load_obj(snl_scene *, const char *objPath, const char *mtlPath, const char *texDir,
 					   int flipNormalsFlag, int buildFlags);
 

@@ -22,7 +22,7 @@ ABI_SYMBOLS = [
     "snl_trace_rays", "snl_trace_shadow", "snl_raytrace", "snl_render", "snl_render_dev", "snl_scene_sync",
     "snl_scene_launch_count", "snl_scene_stream", "snl_host_scene_load_obj", "snl_host_scene_free",
     "snl_host_scene_counts", "snl_host_scene_copy", "snl_host_scene_material", "snl_host_scene_texture",
-    "snl_scene_set_host_scene", "snl_frame_create", "snl_frame_open", "snl_frame_close", "snl_frame_read",
+    "snl_scene_set_host_scene", "snl_scene_build_device", "snl_scene_build_ms", "snl_frame_create", "snl_frame_open", "snl_frame_close", "snl_frame_read",
 ]
 
 # reference record layouts (src/bvh/tree.h:60-72, src/triangle.h:133-135,181-230)
@@ -32,6 +32,7 @@ TRI_DTYPE = np.dtype([("a", "<f4", 3), ("ba", "<f4", 3), ("ca", "<f4", 3), ("t0"
 SHTRI_DTYPE = np.dtype([("uv", "<f4", (3, 2)), ("nrm", "<f4", (3, 3)), ("mat", "<i4")])
 
 NO_SHADING_DATA, FAST_BUILD, USE_SAH = 1, 2, 4
+BUILD_DEVICE = 8  # ours: tree built on the GPU (snl_scene_build_device)
 MAT_SIMPLE, MAT_UBER, MAT_TEX, MAT_TRANSPARENT = 0, 1, 2, 3
 
 
@@ -111,6 +112,9 @@ def load_library(counters: bool = False) -> C.CDLL:
     L.snl_scene_destroy.argtypes = [vp]
     L.snl_scene_destroy.restype = None
     L.snl_scene_set_geometry.argtypes = [vp, vp, i, vp, vp, i, vp, i]
+    L.snl_scene_build_device.argtypes = [vp, vp, vp, i, vp, i]
+    L.snl_scene_build_ms.argtypes = [vp]
+    L.snl_scene_build_ms.restype = C.c_float
     L.snl_scene_set_materials.argtypes = [vp, vp, i, vp, i]
     L.snl_scene_set_lights.argtypes = [vp, vp, i, vp]
     L.snl_set_options.argtypes = [vp, vp]
@@ -245,6 +249,20 @@ class Scene:
         matids = np.ascontiguousarray(matids if matids is not None else [], np.int32)
         self._check(self.L.snl_scene_set_geometry(self.h, _ptr(nodes), len(nodes), _ptr(tris), _ptr(shtris), len(tris),
                                                   _ptr(matids) if len(matids) else None, len(matids)))
+
+    def build_device(self, tris, shtris=None, matids=None):
+        """Triangle soup (reference layouts, any order) -> BVH built on the GPU (snl_scene_build_device)."""
+        tris = np.ascontiguousarray(tris)
+        assert tris.dtype.itemsize == 64
+        if shtris is not None:
+            shtris = np.ascontiguousarray(shtris)
+            assert shtris.dtype.itemsize == 64 and len(shtris) == len(tris)
+        matids = np.ascontiguousarray(matids if matids is not None else [], np.int32)
+        self._check(self.L.snl_scene_build_device(self.h, _ptr(tris), _ptr(shtris), len(tris),
+                                                  _ptr(matids) if len(matids) else None, len(matids)))
+
+    def build_ms(self) -> float:
+        return float(self.L.snl_scene_build_ms(self.h))
 
     def set_materials(self, materials, textures=()):
         """materials: list of dict(kind, flags, color, specular, opacity, texture); textures: list of

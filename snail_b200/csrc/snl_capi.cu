@@ -350,8 +350,69 @@ void snl_scene_destroy(snl_scene *s) {
 	delete s;
 }
 
+static std::vector<GenTri> gen_tris(const HostBVH &h) {
+	const int nTris = (int)h.tris.size();
+	std::vector<GenTri> gt(nTris);
+	for(int i = 0; i < nTris; i++) {
+		const RefTriangle &t = h.tris[i];
+		gt[i].a = {t.a[0], t.a[1], t.a[2], t.it0};
+		gt[i].ba = {t.ba[0], t.ba[1], t.ba[2], 0.0f};
+		gt[i].ca = {t.ca[0], t.ca[1], t.ca[2], 0.0f};
+		gt[i].n = {t.plane[0], t.plane[1], t.plane[2], 0.0f};
+	}
+	return gt;
+}
+
+// HostBVH without nodes: the triangles are a soup in file order and the tree is built on the device (snl_build.cu).
+static int build_geometry_on_device(snl_scene *s) {
+	const HostBVH &h = s->host;
+	const int nTris = (int)h.tris.size();
+	const std::vector<GenTri> gt = gen_tris(h);
+	SNL_CUDA(cudaStreamSynchronize(s->stream));
+	DevBuf<GenTri> inTris;
+	DevBuf<RefShTri> inSh;
+	SNL_CUDA(inTris.reserve(nTris));
+	SNL_CUDA(cudaMemcpy(inTris.ptr, gt.data(), (size_t)nTris * sizeof(GenTri), cudaMemcpyHostToDevice));
+	s->hasShading = !h.shTris.empty();
+	if(s->hasShading) {
+		SNL_CUDA(inSh.reserve(nTris));
+		SNL_CUDA(cudaMemcpy(inSh.ptr, h.shTris.data(), (size_t)nTris * sizeof(RefShTri), cudaMemcpyHostToDevice));
+		SNL_CUDA(s->dShTris.reserve(nTris));
+	}
+	SNL_CUDA(s->dTris.reserve(nTris));
+	SNL_CUDA(s->dNodes.reserve(std::max(nTris - 1, 1)));
+	int height = 0, launches = 0;
+	cudaError_t err = device_build_lbvh(inTris.ptr, s->hasShading ? inSh.ptr : nullptr, nTris, s->dTris.ptr,
+										s->hasShading ? s->dShTris.ptr : nullptr, s->dNodes.ptr, &height, s->devBBox, s->stream,
+										&launches, &s->buildMs);
+	inTris.release();
+	inSh.release();
+	if(err != cudaSuccess) {
+		set_error("device BVH build failed: %s", cudaGetErrorString(err));
+		return SNL_ERR_CUDA;
+	}
+	s->launches += launches;
+	SNL_REQUIRE(height <= kStack - 2, SNL_ERR_UNSUPPORTED, "device-built tree depth %d exceeds the traversal stack (%d)",
+				height, kStack - 2);
+	s->nTriMat = (int)h.triMatId.size();
+	SNL_CUDA(s->dTriMat.reserve(std::max(1, s->nTriMat)));
+	if(s->nTriMat)
+		SNL_CUDA(cudaMemcpy(s->dTriMat.ptr, h.triMatId.data(), s->nTriMat * sizeof(int), cudaMemcpyHostToDevice));
+	s->nTris = nTris;
+	s->nGpuNodes = std::max(nTris - 1, 1);
+	s->gpuDepth = height;
+	s->devBuilt = true;
+	for(auto &e : s->lightPre)
+		e.valid = false;
+	s->originPre.valid = false;
+	return SNL_OK;
+}
+
 static int upload_geometry(snl_scene *s) {
 	const HostBVH &h = s->host;
+	if(h.nodes.empty() && !h.tris.empty())
+		return build_geometry_on_device(s);
+	s->devBuilt = false;
 	Flattener f(h.nodes);
 	SNL_REQUIRE(f.run(), SNL_ERR_INVALID, "malformed BVH::Node array (child / triangle range out of bounds)");
 	SNL_REQUIRE(f.maxDepth <= kStack - 2, SNL_ERR_UNSUPPORTED, "tree depth %d exceeds the traversal stack (%d)",
@@ -363,14 +424,7 @@ static int upload_geometry(snl_scene *s) {
 		}
 
 	const int nTris = (int)h.tris.size();
-	std::vector<GenTri> gt(nTris);
-	for(int i = 0; i < nTris; i++) {
-		const RefTriangle &t = h.tris[i];
-		gt[i].a = {t.a[0], t.a[1], t.a[2], t.it0};
-		gt[i].ba = {t.ba[0], t.ba[1], t.ba[2], 0.0f};
-		gt[i].ca = {t.ca[0], t.ca[1], t.ca[2], 0.0f};
-		gt[i].n = {t.plane[0], t.plane[1], t.plane[2], 0.0f};
-	}
+	const std::vector<GenTri> gt = gen_tris(h);
 	SNL_CUDA(cudaStreamSynchronize(s->stream));
 	SNL_CUDA(s->dNodes.reserve(f.out.size()));
 	SNL_CUDA(cudaMemcpy(s->dNodes.ptr, f.out.data(), f.out.size() * sizeof(GpuNode), cudaMemcpyHostToDevice));
@@ -413,6 +467,27 @@ int snl_scene_set_geometry(snl_scene *s, const void *nodes, int nNodes, const vo
 	h.depth = 0;
 	return upload_geometry(s);
 }
+
+int snl_scene_build_device(snl_scene *s, const void *tris, const void *shTris, int nTris, const int *triMatId, int nMatIds) {
+	SNL_REQUIRE(s && tris, SNL_ERR_INVALID, "null argument");
+	SNL_REQUIRE(nTris > 0, SNL_ERR_INVALID, "empty geometry (nTris=%d)", nTris);
+	SNL_REQUIRE(nTris <= (1 << kLeafFirstBits), SNL_ERR_UNSUPPORTED, "more than 2^26 triangles");
+	SNL_REQUIRE(nMatIds >= 0 && (nMatIds == 0 || triMatId), SNL_ERR_INVALID, "bad material id table");
+	SNL_CUDA(cudaSetDevice(s->device));
+	HostBVH &h = s->host;
+	h.nodes.clear();
+	h.tris.assign((const RefTriangle *)tris, (const RefTriangle *)tris + nTris);
+	if(shTris)
+		h.shTris.assign((const RefShTri *)shTris, (const RefShTri *)shTris + nTris);
+	else
+		h.shTris.clear();
+	h.triMatId.assign(triMatId, triMatId + nMatIds);
+	h.matNames.clear();
+	h.depth = 0;
+	return upload_geometry(s);
+}
+
+float snl_scene_build_ms(snl_scene *s) { return s ? s->buildMs : 0.0f; }
 
 static int upload_materials(snl_scene *s, const snl_material *mats, int nMats, const snl_texture *tex, int nTex) {
 	SNL_CUDA(cudaSetDevice(s->device));
@@ -510,13 +585,13 @@ int snl_set_options(snl_scene *s, const int gVals[16]) {
 int snl_scene_counts(snl_scene *s, int *nNodes, int *nTris, int *nMatIds, int *depth, int *nMaterials) {
 	SNL_REQUIRE(s, SNL_ERR_INVALID, "null scene");
 	if(nNodes)
-		*nNodes = (int)s->host.nodes.size();
+		*nNodes = s->devBuilt ? s->nGpuNodes : (int)s->host.nodes.size();
 	if(nTris)
 		*nTris = (int)s->host.tris.size();
 	if(nMatIds)
 		*nMatIds = (int)s->host.triMatId.size();
 	if(depth)
-		*depth = s->host.depth;
+		*depth = s->devBuilt ? s->gpuDepth : s->host.depth;
 	if(nMaterials)
 		*nMaterials = s->nMats;
 	return SNL_OK;
@@ -524,6 +599,7 @@ int snl_scene_counts(snl_scene *s, int *nNodes, int *nTris, int *nMatIds, int *d
 
 int snl_scene_copy_host_bvh(snl_scene *s, void *nodes, void *tris, void *shTris, int *triMatId) {
 	SNL_REQUIRE(s, SNL_ERR_INVALID, "null scene");
+	SNL_REQUIRE(!s->devBuilt, SNL_ERR_STATE, "the tree was built on the device: there is no BVH::Node array to copy");
 	const HostBVH &h = s->host;
 	if(nodes)
 		memcpy(nodes, h.nodes.data(), h.nodes.size() * sizeof(RefNode));
@@ -537,7 +613,12 @@ int snl_scene_copy_host_bvh(snl_scene *s, void *nodes, void *tris, void *shTris,
 }
 
 int snl_scene_bbox(snl_scene *s, float bmin[3], float bmax[3]) {
-	SNL_REQUIRE(s && !s->host.nodes.empty(), SNL_ERR_STATE, "no geometry");
+	SNL_REQUIRE(s && s->nGpuNodes > 0, SNL_ERR_STATE, "no geometry");
+	if(s->devBuilt) {
+		memcpy(bmin, s->devBBox, 12);
+		memcpy(bmax, s->devBBox + 3, 12);
+		return SNL_OK;
+	}
 	memcpy(bmin, s->host.nodes[0].bmin, 12);
 	memcpy(bmax, s->host.nodes[0].bmax, 12);
 	return SNL_OK;

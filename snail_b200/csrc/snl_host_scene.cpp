@@ -593,19 +593,25 @@ struct Builder {
 bool build_bvh(const Object &obj, const std::map<std::string, int> &matNames, int flags, HostBVH &bvh, std::string &err) {
 	bvh = HostBVH();
 	to_tri_vectors(obj, !(flags & kNoShadingData), bvh.tris, bvh.shTris);
-	bvh.nodes.reserve(bvh.tris.size() * 2);
-	Box bbox = tri_box(bvh.tris[0]);
-	for(size_t n = 1; n < bvh.tris.size(); n++)
-		box_add(bbox, tri_box(bvh.tris[n]));
-	Builder b{bvh, (flags & kUseSah) != 0};
-	b.push_node(bbox);
-	if(flags & kFastBuild)  // src/bvh/tree.cpp:311-314
-		b.split_binned(0, 0, (int)bvh.tris.size(), 0);
-	else
-		b.split(0, 0, (int)bvh.tris.size(), 0);
-	if(bvh.depth > Builder::maxDepth) {
-		err = "BVH deeper than maxDepth";
+	if(bvh.tris.empty()) {
+		err = "no triangles";
 		return false;
+	}
+	if(!(flags & kDeviceBuild)) {  // kDeviceBuild: triangles stay in file order, nodes stay empty (snl_build.cu builds)
+		bvh.nodes.reserve(bvh.tris.size() * 2);
+		Box bbox = tri_box(bvh.tris[0]);
+		for(size_t n = 1; n < bvh.tris.size(); n++)
+			box_add(bbox, tri_box(bvh.tris[n]));
+		Builder b{bvh, (flags & kUseSah) != 0};
+		b.push_node(bbox);
+		if(flags & kFastBuild)  // src/bvh/tree.cpp:311-314
+			b.split_binned(0, 0, (int)bvh.tris.size(), 0);
+		else
+			b.split(0, 0, (int)bvh.tris.size(), 0);
+		if(bvh.depth > Builder::maxDepth) {
+			err = "BVH deeper than maxDepth";
+			return false;
+		}
 	}
 	// BVH::materials names, indexed by the OBJ's material id (src/bvh/tree.cpp:316-327)
 	bvh.matNames.assign(matNames.size(), std::string());

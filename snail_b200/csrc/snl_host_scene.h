@@ -42,6 +42,7 @@ struct HostScene {
 };
 
 enum { kNoShadingData = 1, kFastBuild = 2, kUseSah = 4 };  // src/bvh/tree.h:21-25
+enum { kDeviceBuild = 8 };  // ours: leave HostBVH::nodes empty, the tree is built on the GPU (snl_build.cu)
 
 // Returns false and fills err on failure.
 bool load_obj_scene(const char *objPath, const char *mtlPath, const char *texDir, int flipNormalsFlag, int buildFlags,

@@ -30,4 +30,11 @@ cudaError_t launch_render_wavefront(const SceneDev &S, const PreSet &pre, const 
 									const int4 *packets, int nPackets, const WfBuffers &B, int persistentCtas,
 									unsigned char *out, size_t pitch, cudaStream_t st, int *launches);
 
+// Device-side BVH build (snl_build.cu): Morton-order LBVH over `n` triangles. Writes the triangles / shading records
+// in leaf order, max(n-1, 1) GpuNode records (node 0 = root), the inner-node height of the tree and the scene box
+// {min xyz, max xyz}. Synchronises the stream. *kernelMs = device time of the kernels (events on `st`).
+cudaError_t device_build_lbvh(const GenTri *inTris, const RefShTri *inSh, int n, GenTri *outTris, RefShTri *outSh,
+							  GpuNode *outNodes, int *heightOut, float bboxOut[6], cudaStream_t st, int *launches,
+							  float *kernelMs);
+
 }  // namespace snl

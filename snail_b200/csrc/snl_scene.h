@@ -62,6 +62,9 @@ struct snl_scene {
 	// reference-layout host copies (kept for snl_scene_copy_host_bvh and re-flattening)
 	snl::HostBVH host;
 	int nTris = 0, nGpuNodes = 0, gpuDepth = 0;
+	bool devBuilt = false;     // tree built by snl_build.cu (host.nodes is empty)
+	float devBBox[6] = {0};    // its scene box
+	float buildMs = 0.0f;      // device time of the last device build
 
 	snl::DevBuf<snl::GpuNode> dNodes;
 	snl::DevBuf<snl::GenTri> dTris;
