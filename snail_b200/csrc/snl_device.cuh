@@ -162,6 +162,15 @@ __device__ __forceinline__ void tri_nearest_gen(const GenTri *__restrict__ t, in
 
 enum { kSentinel = 0x7fffffff };
 
+// SNL_REL_NODES: shared-origin rays walk a per-origin copy of the nodes with boxes translated by the origin (one FMUL
+// per slab plane). Default off: with the slab test written as one FMA per plane every ray walks the ONE node array,
+// which costs the same instructions and keeps a third of the node bytes in L1 / L2.
+#ifdef SNL_REL_NODES
+constexpr bool kRelNodes = true;
+#else
+constexpr bool kRelNodes = false;
+#endif
+
 // One step of the walk after the two box tests of the node at `cur`: go to the nearer hit child (push the farther), or
 // pop; a leaf reached while none is parked gets parked and the walk continues with the next stack entry. stack[-1]
 // reads (sp == 0 when tos is the sentinel) cannot happen: the sentinel ends the walk before it would be popped twice.
@@ -261,7 +270,7 @@ __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nod
 			bool h0, h1;
 			float lmin0, lmin1;
 			int l0, l1;
-			node_test<SHARED>(nodes + cur, bx, by, bz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
+			node_test<SHARED && kRelNodes>(nodes + cur, bx, by, bz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
 			SNL_TRAVERSE_STEP();
 			if(!__any_sync(__activemask(), leaf == 0))
 				break;
@@ -289,8 +298,14 @@ __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nod
 // BVH::TraverseShadow per ray (src/bvh/traverse.cpp:82-149) with Triangle::Collide(ShadowContext&)
 // (src/triangle.cpp:65-102): any hit, ONE-SIDED (only triangles with dir.nrm >= u+v >= 0 occlude), no division.
 // Origin = light position: nodes are that light's translated boxes, triangles its PreTri records.
-__device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ nodes, const PreTri *__restrict__ tris, float dx,
-												float dy, float dz, float ix, float iy, float iz, float dist, TravCount &tc) {
+__device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ nodes, const PreTri *__restrict__ tris, float ox,
+												float oy, float oz, float dx, float dy, float dz, float ix, float iy, float iz,
+												float dist, TravCount &tc) {
+#ifndef SNL_BOX_EXACT
+	const float bx = ox * ix, by = oy * iy, bz = oz * iz;  // box_test's origin * idir
+#else
+	const float bx = ox, by = oy, bz = oz;
+#endif
 	SNL_STACK_DECL();
 	int cur = 0;
 	bool occluded = false;
@@ -301,7 +316,7 @@ __device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ node
 			bool h0, h1;
 			float lmin0, lmin1;
 			int l0, l1;
-			node_test<true>(nodes + cur, 0.0f, 0.0f, 0.0f, ix, iy, iz, dist, h0, h1, lmin0, lmin1, l0, l1);
+			node_test<kRelNodes>(nodes + cur, bx, by, bz, ix, iy, iz, dist, h0, h1, lmin0, lmin1, l0, l1);
 			SNL_TRAVERSE_STEP();
 			if(!__any_sync(__activemask(), leaf == 0))
 				break;
@@ -626,8 +641,8 @@ __device__ __forceinline__ bool trace_light(const SceneDev &S, int li, bool sel,
 	if(!light_setup(L, s.px, s.py, s.pz, s.nx, s.ny, s.nz, fx, fy, fz, dot, distance))
 		return false;
 	const float tmax = distance * 0.9999f;
-	const bool occluded = traverse_shadow(S.lightPre[li].nodes, S.lightPre[li].tris, fx, fy, fz, safe_inv(fx), safe_inv(fy),
-										  safe_inv(fz), tmax, tc);
+	const bool occluded = traverse_shadow(kRelNodes ? S.lightPre[li].nodes : S.nodes, S.lightPre[li].tris, L.pos[0], L.pos[1],
+										  L.pos[2], fx, fy, fz, safe_inv(fx), safe_inv(fy), safe_inv(fz), tmax, tc);
 	if(!occluded && tmax > 0.0f)
 		light_accumulate(L, dot, distance, ldr, ldg, ldb, lsr, lsg, lsb);
 	return true;
@@ -741,7 +756,7 @@ __device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet o
 	if(active) {
 		const float ix = safe_inv(dx), iy = safe_inv(dy), iz = safe_inv(dz);
 		if(SHARED)
-			traverse_nearest<true>(originPre.nodes, originPre.tris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
+			traverse_nearest<true>(kRelNodes ? originPre.nodes : S.nodes, originPre.tris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
 		else
 			traverse_nearest<false>(S.nodes, S.gtris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
 		if(!DEPTH0)

@@ -11,7 +11,7 @@ __global__ void __launch_bounds__(256) k_pretransform(const GenTri *__restrict__
 													 const GpuNode *__restrict__ nodes, int nNodes, float ox, float oy,
 													 float oz, PreTri *__restrict__ out, GpuNode *__restrict__ outNodes) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
-	if(i < nNodes) {
+	if(outNodes && i < nNodes) {  // only with SNL_REL_NODES (snl_device.cuh)
 		const float4 b0 = ldg4(&nodes[i].b0), b1 = ldg4(&nodes[i].b1), bz = ldg4(&nodes[i].bz);
 		const int4 link = ldg4(&nodes[i].link);
 		float4 *o = reinterpret_cast<float4 *>(outNodes + i);
@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(kPacket) k_primary(SceneDev S, const PreSet pr
 		h.dist = CUDART_INF_F;
 		h.obj = 0;
 		h.bu = h.bv = 0.0f;
-		traverse_nearest<true>(pre.nodes, pre.tris, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, safe_inv(dx), safe_inv(dy),
+		traverse_nearest<true>(kRelNodes ? pre.nodes : S.nodes, pre.tris, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, safe_inv(dx), safe_inv(dy),
 							   safe_inv(dz), h, tc);
 		pc.primary = 1;
 		const size_t o = (size_t)y * W + x;
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(kPacket) k_trace_rays(SceneDev S, const PreSet
 			const float *o = SHARED ? o3 : o3 + (size_t)i * 3;
 			const float ox = o[0], oy = o[1], oz = o[2];
 			const float dx = d3[(size_t)i * 3 + 0], dy = d3[(size_t)i * 3 + 1], dz = d3[(size_t)i * 3 + 2];
-			traverse_nearest<SHARED>(SHARED ? pre.nodes : S.nodes, SHARED ? (const void *)pre.tris : (const void *)S.gtris, ox, oy, oz, dx, dy, dz,
+			traverse_nearest<SHARED>(SHARED && kRelNodes ? pre.nodes : S.nodes, SHARED ? (const void *)pre.tris : (const void *)S.gtris, ox, oy, oz, dx, dy, dz,
 									 safe_inv(dx), safe_inv(dy), safe_inv(dz), h, tc);
 			pc.primary = 1;
 		}
@@ -126,7 +126,8 @@ __global__ void __launch_bounds__(kPacket) k_trace_shadow(SceneDev S, const PreS
 		const float dist = tmax[i];
 		if(dist >= 0.0f) {
 			const float dx = d3[(size_t)i * 3 + 0], dy = d3[(size_t)i * 3 + 1], dz = d3[(size_t)i * 3 + 2];
-			if(traverse_shadow(pre.nodes, pre.tris, dx, dy, dz, safe_inv(dx), safe_inv(dy), safe_inv(dz), dist, tc))
+			if(traverse_shadow(kRelNodes ? pre.nodes : S.nodes, pre.tris, ox, oy, oz, dx, dy, dz, safe_inv(dx), safe_inv(dy),
+							   safe_inv(dz), dist, tc))
 				tmax[i] = -CUDART_INF_F;
 			pc.shadow = 1;
 		}
@@ -252,6 +253,10 @@ cudaError_t launch_pretransform(const GenTri *gtris, int nTris, const GpuNode *n
 								PreTri *out, GpuNode *outNodes, cudaStream_t st) {
 	if(nTris <= 0)
 		return cudaSuccess;
+	if(!kRelNodes) {
+		outNodes = nullptr;
+		nNodes = 0;
+	}
 	k_pretransform<<<blocks_for(nTris > nNodes ? nTris : nNodes, 256), 256, 0, st>>>(gtris, nTris, nodes, nNodes, origin[0],
 																					 origin[1], origin[2], out, outNodes);
 	return cudaGetLastError();

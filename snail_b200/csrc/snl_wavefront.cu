@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(kPacket) k_wf_primary(SceneDev S, const PreSet
 	h.dist = CUDART_INF_F;
 	h.obj = 0;
 	h.bu = h.bv = 0.0f;
-	traverse_nearest<true>(pre.nodes, pre.tris, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, safe_inv(dx), safe_inv(dy),
+	traverse_nearest<true>(kRelNodes ? pre.nodes : S.nodes, pre.tris, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, safe_inv(dx), safe_inv(dy),
 						   safe_inv(dz), h, tc);
 	pc.primary = 1;
 	__syncwarp();
@@ -187,7 +187,10 @@ __global__ void __launch_bounds__(256, SNL_WF_MIN_BLOCKS) k_wf_trace(SceneDev S,
 					dz = r.z;
 					h.dist = r.w;  // tmax
 					const PreSet ps = B.lightSets[li];
-					nodes = ps.nodes;
+					nodes = kRelNodes ? ps.nodes : S.nodes;
+					ox = S.lights[li].pos[0];  // the shadow rays start at the light (box_test needs the origin)
+					oy = S.lights[li].pos[1];
+					oz = S.lights[li].pos[2];
 					ptris = ps.tris;
 				}
 				else {
@@ -224,9 +227,9 @@ __global__ void __launch_bounds__(256, SNL_WF_MIN_BLOCKS) k_wf_trace(SceneDev S,
 			float lmin0, lmin1;
 			int l0, l1;
 #ifndef SNL_BOX_EXACT  // box_test takes origin * idir (loop-invariant: hoisted out of the walk)
-			node_test<SHADOW>(nodes + cur, ox * ix, oy * iy, oz * iz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
+			node_test<SHADOW && kRelNodes>(nodes + cur, ox * ix, oy * iy, oz * iz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
 #else
-			node_test<SHADOW>(nodes + cur, ox, oy, oz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
+			node_test<SHADOW && kRelNodes>(nodes + cur, ox, oy, oz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
 #endif
 			SNL_TRAVERSE_STEP();
 			if(!__any_sync(__activemask(), leaf == 0))
