@@ -179,8 +179,11 @@ __device__ __forceinline__ unsigned conv_channel(float c) {
 #endif
 // TRANSP: the scene has a material that can start a transparency pass. SUPER: gVals[9], every 16x16 output packet is
 // traced as four 16x16 packets of the 2W x 2H image and box-filtered (src/render.cpp:71-110).
-template <bool TRANSP, bool SUPER>
-__global__ void __launch_bounds__(kPacket, SNL_RENDER_MIN_BLOCKS) k_render(SceneDev S, const PreSet pre, RayGenParams g, int W, int H,
+// MINB: resident CTAs per SM the register allocation aims for. 4 (64 registers) suits scenes whose hot set sits in L1;
+// 5 (48 registers, a few more spills) hides more latency on large scenes: +1.9 % on sponza_like, -2 % on feline.
+// The scene picks per workload by timing both on its first frames (snl_capi.cu render_common).
+template <bool TRANSP, bool SUPER, int MINB>
+__global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreSet pre, RayGenParams g, int W, int H,
 												 int packetsX, const int4 *__restrict__ packets,
 												 unsigned char *__restrict__ out, size_t pitch) {
 	int px0, py0, cw, ch;
@@ -308,21 +311,24 @@ cudaError_t launch_raytrace(const SceneDev &S, const PreSet &pre, const float *o
 }
 
 cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, const int4 *packets,
-						  int nPackets, unsigned char *out, size_t pitch, cudaStream_t st) {
+						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st) {
 	const int px = (W + 15) / 16, py = (H + 15) / 16;
 	const int grid = packets ? nPackets : px * py;
 	if(grid <= 0)
 		return cudaSuccess;
+	const int MB = SNL_RENDER_MIN_BLOCKS;
 	if(S.hasTransp) {
 		if(S.gvSuper)
-			k_render<true, true><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+			k_render<true, true, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
 		else
-			k_render<true, false><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+			k_render<true, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
 	}
 	else if(S.gvSuper)
-		k_render<false, true><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+		k_render<false, true, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+	else if(variant == 1)
+		k_render<false, false, MB + 1><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
 	else
-		k_render<false, false><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+		k_render<false, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
 	return cudaGetLastError();
 }
 

@@ -23,7 +23,7 @@ cudaError_t launch_trace_shadow(const SceneDev &S, const PreSet &pre, const floa
 cudaError_t launch_raytrace(const SceneDev &S, const PreSet &pre, const float *o3, const float *d3,
 							const unsigned char *mask, int n, bool shared, float *rgb3, cudaStream_t st);
 cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, const int4 *packets,
-						  int nPackets, unsigned char *out, size_t pitch, cudaStream_t st);
+						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st);
 
 // Wavefront form of launch_render for frames with the reflection bounce (snl_wavefront.cu). *launches = kernels issued.
 cudaError_t launch_render_wavefront(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H,

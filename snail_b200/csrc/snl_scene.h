@@ -59,6 +59,14 @@ struct snl_scene {
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	bool evPending = false;
 
+	// k_render comes in two register budgets (snl_kernels.cu, MINB); the first frame of a workload is rendered with
+	// both and the faster one is kept (snl_capi.cu render_common). SNL_RENDER_VARIANT=0|1 pins it.
+	struct RenderTune {
+		long long key = -1;  // W, H, packets, options, lights, triangles of the workload the choice was made for
+		float ms[2] = {0.0f, 0.0f};
+		int choice = -1;     // -1: not decided yet
+	} tune;
+
 	// reference-layout host copies (kept for snl_scene_copy_host_bvh and re-flattening)
 	snl::HostBVH host;
 	int nTris = 0, nGpuNodes = 0, gpuDepth = 0;
