@@ -120,6 +120,31 @@ int snl_scene_build_device(snl_scene *, const void *tris, const void *shTris, in
 						   int nMatIds);
 float snl_scene_build_ms(snl_scene *);
 
+/* Instanced two-level BVH: Scene<DBVH> over ObjectInstances of this scene's BVH (src/dbvh/tree.h, the `-instances n`
+ * mode of src/rtracer.cpp:146-178,359-363). snl_instance = the data members of ObjectInstance (:177-178): rotation rows
+ * (orthonormal), translation. Computes every instance's box (ObjectInstance::ComputeBBox), builds the top-level tree
+ * with DBVH::Construct's binned SAH (src/dbvh/tree.cpp:40-173) - same nodes, same element order as the reference - and
+ * from then on snl_render* and snl_trace_primary_inst walk top tree -> instance -> BVH on the device. Like the
+ * reference's Scene<DBVH> (HasShadingData() == 0) an instanced scene is shaded with the simple path: geometric normal
+ * rotated into world space, default material; shadows and the reflection bounce work. n = 0 returns to the plain BVH.
+ * snl_trace_rays / snl_trace_shadow / snl_raytrace and gVals[9] return SNL_ERR_UNSUPPORTED while instanced. */
+typedef struct snl_instance {
+	float rotation[9]; /* rotation[0..2].xyz */
+	float translation[3];
+} snl_instance;
+int snl_scene_set_instances(snl_scene *, const snl_instance *instances, int n);
+/* DBVH::TraversePrimary(Context<1,0>&): instId = Context::object (index into DBVH::elements, i.e. the builder's
+ * order, see snl_scene_copy_dbvh), triId = Context::element. */
+int snl_trace_primary_inst(snl_scene *, const snl_camera *cam, int W, int H, int *instId, int *triId, float *t,
+						   float *bary2);
+/* DBVH::nodes (32-byte DBVH::Node records) and DBVH::elements in the builder's order, with their boxes {min, max}.
+ * Any out pointer may be NULL. */
+int snl_scene_copy_dbvh(snl_scene *, int *nNodes, void *nodes, int *nInstances, snl_instance *elements, float *bboxes6);
+/* The same host builder without a device (ComputeBBox + DBVH::Construct over n instances of a tree with the given
+ * box): nodesOut holds up to 2n DBVH::Node records, elementsOut / bboxes6Out n entries in the builder's order. */
+int snl_host_dbvh_build(const snl_instance *instances, int n, const float treeMin[3], const float treeMax[3],
+						void *nodesOut, int *nNodes, snl_instance *elementsOut, float *bboxes6Out);
+
 /* Scene::materials / texDict (src/scene.h:25-40, src/scene.cpp:12-21). */
 int snl_scene_set_materials(snl_scene *, const snl_material *mats, int nMats, const snl_texture *tex, int nTex);
 

@@ -15,6 +15,7 @@
 #include "rtbase.h"
 #include "base_scene.h"
 #include "bvh/tree.h"
+#include "dbvh/tree.h"
 #include "camera.h"
 #include "mipmap_texture.h"
 #include "ray_generator.h"
@@ -32,6 +33,9 @@ namespace {
 struct RefScene {
 	Scene<BVH> scene;
 	vector<shading::MaterialDesc> matDescs;
+	// instanced form (src/rtracer.cpp:146-178,359-363): a DBVH over ObjectInstances of `scene.geometry`
+	Scene<DBVH> dscene;
+	bool instanced = false;
 };
 
 Camera MakeCamera(const float *c) {
@@ -144,6 +148,7 @@ void ref_set_lights(void *h, const float *l, int n) {
 	lights.clear();
 	for(int i = 0; i < n; i++, l += 7)
 		lights.push_back(Light(Vec3f(l[0], l[1], l[2]), Vec3f(l[3], l[4], l[5]), l[6]));
+	((RefScene *)h)->dscene.lights = lights;
 }
 
 // cam: pos.xyz right.xyz up.xyz front.xyz plane_dist. out: H rows of 3*W bytes, byte order of
@@ -153,7 +158,8 @@ double ref_render(void *h, const float *cam, int W, int H, int threads, unsigned
 	MipmapTexture image(W, H, fwk::GlFormat::rgb8, 1);
 	memset(image.DataPointer(), 0, image.Size());
 	auto t0 = std::chrono::steady_clock::now();
-	TreeStats st = Render(rs->scene, MakeCamera(cam), image, Options(), (uint)threads);
+	TreeStats st = rs->instanced ? Render(rs->dscene, MakeCamera(cam), image, Options(), (uint)threads)
+								 : Render(rs->scene, MakeCamera(cam), image, Options(), (uint)threads);
 	auto t1 = std::chrono::steady_clock::now();
 	if(out)
 		for(int y = 0; y < H; y++)
@@ -364,6 +370,104 @@ const char *ref_backend() {
 #else
 	return "scalar";
 #endif
+}
+
+// ---- instanced two-level BVH (DBVH, src/dbvh/tree.h) ---------------------------------------------------------------
+// inst: n x {rotation[0..2] (3 x Vec3f), translation}: 12 floats each, the data members of ObjectInstance
+// (src/dbvh/tree.h:177-178). Builds DBVH(instances) over this scene's BVH exactly as MakeDBVH does
+// (ComputeBBox per instance, then the DBVH constructor) and routes ref_render / ref_trace_primary_inst to Scene<DBVH>.
+void ref_scene_set_instances(void *h, const float *inst, int n) {
+	RefScene *rs = (RefScene *)h;
+	rs->instanced = n > 0;
+	if(!n)
+		return;
+	vector<ObjectInstance> instances;
+	for(int i = 0; i < n; i++, inst += 12) {
+		ObjectInstance oi;
+		oi.tree = &rs->scene.geometry;
+		oi.rotation[0] = Vec3f(inst[0], inst[1], inst[2]);
+		oi.rotation[1] = Vec3f(inst[3], inst[4], inst[5]);
+		oi.rotation[2] = Vec3f(inst[6], inst[7], inst[8]);
+		oi.translation = Vec3f(inst[9], inst[10], inst[11]);
+		oi.ComputeBBox();
+		instances.push_back(oi);
+	}
+	rs->dscene.geometry = DBVH(instances);
+	rs->dscene.materials = rs->scene.materials;
+	rs->dscene.lights = rs->scene.lights;
+}
+
+int ref_dbvh_counts(void *h, int *nNodes, int *nInstances) {
+	RefScene *rs = (RefScene *)h;
+	*nNodes = (int)rs->dscene.geometry.nodes.size();
+	*nInstances = (int)rs->dscene.geometry.elements.size();
+	return (int)sizeof(DBVH::Node);
+}
+const void *ref_dbvh_nodes(void *h) { return ((RefScene *)h)->dscene.geometry.nodes.data(); }
+// elements in the DBVH's own order (std::partition moved them): out = n x {rotation 9, translation 3, bbox min 3, max 3}
+void ref_dbvh_elements(void *h, float *out) {
+	for(const ObjectInstance &e : ((RefScene *)h)->dscene.geometry.elements) {
+		for(int r = 0; r < 3; r++) {
+			*out++ = e.rotation[r].x;
+			*out++ = e.rotation[r].y;
+			*out++ = e.rotation[r].z;
+		}
+		*out++ = e.translation.x;
+		*out++ = e.translation.y;
+		*out++ = e.translation.z;
+		*out++ = e.bbox.min.x;
+		*out++ = e.bbox.min.y;
+		*out++ = e.bbox.min.z;
+		*out++ = e.bbox.max.x;
+		*out++ = e.bbox.max.y;
+		*out++ = e.bbox.max.z;
+	}
+}
+
+// ref_trace_primary on the instanced scene: instId = Context::object (index into DBVH::elements), triId = element.
+void ref_trace_primary_inst(void *h, const float *cam, int W, int H, int *instId, int *triId, float *t, float *bary) {
+	RefScene *rs = (RefScene *)h;
+	Camera camera = MakeCamera(cam);
+	RayGenerator rayGen(3, W, H, camera.plane_dist, camera.right, camera.up, camera.front);
+	Vec3q origin;
+	Broadcast(camera.pos, origin);
+	for(int y = 0; y < H; y += 16)
+		for(int x = 0; x < W; x += 16) {
+			Vec3q dir[64], idir[64];
+			rayGen.Generate(16, 16, x, y, dir);
+			for(int n = 0; n < 64; n++)
+				idir[n] = SafeInv(dir[n]);
+			floatq dist[64];
+			i32x4 object[64], element[64];
+			Vec2q bar[64];
+			for(int q = 0; q < 64; q++) {
+				dist[q] = floatq(constant::inf);
+				object[q] = i32x4(0);
+				element[q] = i32x4(0);
+				bar[q] = Vec2q(floatq(0.0f), floatq(0.0f));
+			}
+			TreeStats st;
+			RayGroup<1, 0> rays(&origin, dir, idir, 64);
+			Context<1, 0> ctx(rays, dist, object, element, bar, &st);
+			rs->dscene.geometry.TraversePrimary(ctx);
+			for(int q = 0; q < 64; q++) {
+				int py = y + q / 4;
+				if(py >= H)
+					continue;
+				for(int k = 0; k < 4; k++) {
+					int px = x + (q & 3) * 4 + k;
+					if(px >= W)
+						continue;
+					size_t o = (size_t)py * W + px;
+					bool hit = dist[q][k] < constant::inf;
+					instId[o] = hit ? object[q][k] : -1;
+					triId[o] = hit ? element[q][k] : -1;
+					t[o] = dist[q][k];
+					bary[o * 2 + 0] = hit ? bar[q].x[k] : 0.0f;
+					bary[o * 2 + 1] = hit ? bar[q].y[k] : 0.0f;
+				}
+			}
+		}
 }
 
 } // extern "C"

@@ -55,6 +55,12 @@ def lib(variant: str = "scalar") -> C.CDLL:
     L.ref_trace_shadow.argtypes = [C.c_void_p, _f32p, _f32p, _f32p, C.c_int]
     L.ref_raytrace.argtypes = [C.c_void_p, _f32p, _f32p, C.c_void_p, C.c_int, C.c_int, _f32p, _u32p]
     L.ref_primary_dirs.argtypes = [_f32p, C.c_int, C.c_int, _f32p]
+    L.ref_scene_set_instances.argtypes = [C.c_void_p, _f32p, C.c_int]
+    L.ref_dbvh_counts.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.ref_dbvh_nodes.restype = C.c_void_p
+    L.ref_dbvh_nodes.argtypes = [C.c_void_p]
+    L.ref_dbvh_elements.argtypes = [C.c_void_p, _f32p]
+    L.ref_trace_primary_inst.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, _i32p, _i32p, _f32p, _f32p]
     L.ref_backend.restype = C.c_char_p
     _libs[variant] = L
     return L
@@ -124,6 +130,28 @@ class RefScene:
                 self.L.ref_scene_material_texture(self.h, i, tex.ctypes.data)
             out.append(dict(flags=flags, tex_w=w, tex_h=h, tex_mips=mips, tex=tex))
         return out
+
+    # ---- instanced form: Scene<DBVH> over ObjectInstances of this BVH (src/dbvh/tree.h) ------------------------
+    def set_instances(self, instances):
+        """instances: (n, 12) float32 {rotation rows, translation}. Set lights AFTER this or before, either works."""
+        a = np.ascontiguousarray(np.asarray(instances, np.float32).reshape(-1, 12))
+        self.L.ref_scene_set_instances(self.h, a, len(a))
+
+    def dbvh(self):
+        """(DBVH::nodes, elements (n, 12) in DBVH order, boxes (n, 6))."""
+        nn, ni = C.c_int(), C.c_int()
+        assert self.L.ref_dbvh_counts(self.h, C.byref(nn), C.byref(ni)) == 32
+        nodes = self._view(self.L.ref_dbvh_nodes(self.h), nn.value, NODE_DTYPE)
+        e = np.zeros((ni.value, 18), np.float32)
+        self.L.ref_dbvh_elements(self.h, e)
+        return nodes, e[:, :12].copy(), e[:, 12:].copy()
+
+    def trace_primary_inst(self, cam, W, H):
+        cam = np.ascontiguousarray(cam, np.float32)
+        inst, tri = np.zeros((H, W), np.int32), np.zeros((H, W), np.int32)
+        t, bary = np.zeros((H, W), np.float32), np.zeros((H, W, 2), np.float32)
+        self.L.ref_trace_primary_inst(self.h, cam, W, H, inst, tri, t, bary)
+        return inst, tri, t, bary
 
     def bbox(self):
         out = np.zeros(6, np.float32)

@@ -22,7 +22,8 @@ ABI_SYMBOLS = [
     "snl_trace_rays", "snl_trace_shadow", "snl_raytrace", "snl_render", "snl_render_dev", "snl_scene_sync",
     "snl_scene_launch_count", "snl_scene_stream", "snl_host_scene_load_obj", "snl_host_scene_free",
     "snl_host_scene_counts", "snl_host_scene_copy", "snl_host_scene_material", "snl_host_scene_texture",
-    "snl_scene_set_host_scene", "snl_scene_build_device", "snl_scene_build_ms", "snl_frame_create", "snl_frame_open", "snl_frame_close", "snl_frame_read",
+    "snl_scene_set_host_scene", "snl_scene_build_device", "snl_scene_build_ms", "snl_scene_set_instances",
+    "snl_trace_primary_inst", "snl_scene_copy_dbvh", "snl_host_dbvh_build", "snl_frame_create", "snl_frame_open", "snl_frame_close", "snl_frame_read",
 ]
 
 # reference record layouts (src/bvh/tree.h:60-72, src/triangle.h:133-135,181-230)
@@ -112,6 +113,10 @@ def load_library(counters: bool = False) -> C.CDLL:
     L.snl_scene_destroy.argtypes = [vp]
     L.snl_scene_destroy.restype = None
     L.snl_scene_set_geometry.argtypes = [vp, vp, i, vp, vp, i, vp, i]
+    L.snl_scene_set_instances.argtypes = [vp, vp, i]
+    L.snl_trace_primary_inst.argtypes = [vp, vp, i, i, vp, vp, vp, vp]
+    L.snl_scene_copy_dbvh.argtypes = [vp, ip, vp, ip, vp, vp]
+    L.snl_host_dbvh_build.argtypes = [vp, i, vp, vp, vp, ip, vp, vp]
     L.snl_scene_build_device.argtypes = [vp, vp, vp, i, vp, i]
     L.snl_scene_build_ms.argtypes = [vp]
     L.snl_scene_build_ms.restype = C.c_float
@@ -152,6 +157,20 @@ def load_library(counters: bool = False) -> C.CDLL:
 
 def _ptr(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def host_dbvh_build(instances, tree_min, tree_max):
+    """ObjectInstance::ComputeBBox + DBVH::Construct on the host (no device): (nodes, elements, boxes)."""
+    L = load_library()
+    a = np.ascontiguousarray(np.asarray(instances, np.float32).reshape(-1, 12))
+    lo, hi = np.ascontiguousarray(tree_min, np.float32), np.ascontiguousarray(tree_max, np.float32)
+    nodes = np.zeros(2 * len(a), NODE_DTYPE)
+    el, bb = np.zeros((len(a), 12), np.float32), np.zeros((len(a), 6), np.float32)
+    nn = C.c_int()
+    r = L.snl_host_dbvh_build(_ptr(a), len(a), _ptr(lo), _ptr(hi), _ptr(nodes), C.byref(nn), _ptr(el), _ptr(bb))
+    if r:
+        raise SnlError(r, L.snl_last_error().decode())
+    return nodes[: nn.value], el, bb
 
 
 class HostScene:
@@ -260,6 +279,26 @@ class Scene:
         matids = np.ascontiguousarray(matids if matids is not None else [], np.int32)
         self._check(self.L.snl_scene_build_device(self.h, _ptr(tris), _ptr(shtris), len(tris),
                                                   _ptr(matids) if len(matids) else None, len(matids)))
+
+    def set_instances(self, instances):
+        """instances: (n, 12) float32 = ObjectInstance {rotation rows (9), translation (3)}; n = 0: plain BVH again."""
+        a = np.ascontiguousarray(np.asarray(instances, np.float32).reshape(-1, 12))
+        self._check(self.L.snl_scene_set_instances(self.h, _ptr(a) if len(a) else None, len(a)))
+
+    def dbvh(self):
+        """(DBVH::nodes as NODE_DTYPE records, elements (n, 12) in the builder's order, boxes (n, 6))."""
+        nn, ni = C.c_int(), C.c_int()
+        self._check(self.L.snl_scene_copy_dbvh(self.h, C.byref(nn), None, C.byref(ni), None, None))
+        nodes = np.zeros(nn.value, NODE_DTYPE)
+        el, bb = np.zeros((ni.value, 12), np.float32), np.zeros((ni.value, 6), np.float32)
+        self._check(self.L.snl_scene_copy_dbvh(self.h, None, _ptr(nodes), None, _ptr(el), _ptr(bb)))
+        return nodes, el, bb
+
+    def trace_primary_inst(self, cam: Camera, W, H):
+        inst, tri = np.zeros((H, W), np.int32), np.zeros((H, W), np.int32)
+        t, bary = np.zeros((H, W), np.float32), np.zeros((H, W, 2), np.float32)
+        self._check(self.L.snl_trace_primary_inst(self.h, C.byref(cam), W, H, _ptr(inst), _ptr(tri), _ptr(t), _ptr(bary)))
+        return inst, tri, t, bary
 
     def build_ms(self) -> float:
         return float(self.L.snl_scene_build_ms(self.h))

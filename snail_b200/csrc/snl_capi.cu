@@ -44,6 +44,8 @@ void set_error(const char *fmt, ...) {
 
 namespace {
 
+enum { kTopStackHost = 66 };  // = kTopStack of snl_device.cuh (DBVH::maxDepth + 2)
+
 // ---- flatten: BVH::Node[] (own box per node) -> GpuNode[] (both child boxes per inner node) -------------------
 
 struct Flattener {
@@ -205,6 +207,8 @@ int make_scene_dev(snl_scene *s, SceneDev &S) {
 	S.mats = s->dMats.ptr;
 	S.nMats = s->nMats;
 	S.texs = s->dTexs.ptr;
+	S.topNodes = s->instances.empty() ? nullptr : s->dTopNodes.ptr;
+	S.instances = s->instances.empty() ? nullptr : s->dInstances.ptr;
 	S.nLights = (int)s->lights.size();
 	for(int i = 0; i < S.nLights; i++) {
 		const snl_light &l = s->lights[i];
@@ -306,6 +310,8 @@ void snl_scene_destroy(snl_scene *s) {
 	cudaSetDevice(s->device);
 	if(s->stream)
 		cudaStreamSynchronize(s->stream);
+	s->dTopNodes.release();
+	s->dInstances.release();
 	s->dNodes.release();
 	s->dTris.release();
 	s->dShTris.release();
@@ -489,6 +495,108 @@ int snl_scene_build_device(snl_scene *s, const void *tris, const void *shTris, i
 
 float snl_scene_build_ms(snl_scene *s) { return s ? s->buildMs : 0.0f; }
 
+int snl_scene_set_instances(snl_scene *s, const snl_instance *inst, int n) {
+	SNL_REQUIRE(s && n >= 0 && (n == 0 || inst), SNL_ERR_INVALID, "bad argument");
+	SNL_REQUIRE(s->nGpuNodes > 0, SNL_ERR_STATE, "no geometry: instances refer to the scene's BVH");
+	SNL_CUDA(cudaSetDevice(s->device));
+	SNL_CUDA(cudaStreamSynchronize(s->stream));
+	s->tune.key = -1;
+	if(n == 0) {
+		s->instances.clear();
+		s->topNodes.clear();
+		return SNL_OK;
+	}
+	float bmin[3], bmax[3];
+	if(int r = snl_scene_bbox(s, bmin, bmax))
+		return r;
+	std::vector<HostInstance> elems(n);
+	for(int i = 0; i < n; i++) {
+		memcpy(elems[i].rot, inst[i].rotation, 36);
+		memcpy(elems[i].tr, inst[i].translation, 12);
+		instance_compute_bbox(elems[i], bmin, bmax);
+	}
+	std::vector<RefNode> nodes;
+	int depth = 0;
+	std::string err;
+	if(!build_dbvh(elems, nodes, depth, err)) {
+		set_error("%s", err.c_str());
+		return SNL_ERR_INVALID;
+	}
+	Flattener f(nodes);
+	SNL_REQUIRE(f.run(), SNL_ERR_INVALID, "malformed DBVH");
+	SNL_REQUIRE(f.maxDepth <= kTopStackHost - 2, SNL_ERR_UNSUPPORTED, "DBVH depth %d exceeds the top-level stack", f.maxDepth);
+	std::vector<DevInstance> di(n);
+	for(int i = 0; i < n; i++) {
+		const HostInstance &e = elems[i];
+		di[i].r0 = {e.rot[0][0], e.rot[0][1], e.rot[0][2], 0.0f};
+		di[i].r1 = {e.rot[1][0], e.rot[1][1], e.rot[1][2], 0.0f};
+		di[i].r2 = {e.rot[2][0], e.rot[2][1], e.rot[2][2], 0.0f};
+		di[i].t = {e.tr[0], e.tr[1], e.tr[2], 0.0f};
+	}
+	SNL_CUDA(s->dTopNodes.reserve(f.out.size()));
+	SNL_CUDA(cudaMemcpy(s->dTopNodes.ptr, f.out.data(), f.out.size() * sizeof(GpuNode), cudaMemcpyHostToDevice));
+	SNL_CUDA(s->dInstances.reserve(n));
+	SNL_CUDA(cudaMemcpy(s->dInstances.ptr, di.data(), (size_t)n * sizeof(DevInstance), cudaMemcpyHostToDevice));
+	s->instances.swap(elems);
+	s->topNodes.swap(nodes);
+	s->topDepth = depth;
+	return SNL_OK;
+}
+
+int snl_host_dbvh_build(const snl_instance *inst, int n, const float treeMin[3], const float treeMax[3], void *nodesOut,
+						int *nNodes, snl_instance *elementsOut, float *bboxes6Out) {
+	SNL_REQUIRE(inst && n > 0 && treeMin && treeMax && nNodes, SNL_ERR_INVALID, "bad argument");
+	std::vector<HostInstance> elems(n);
+	for(int i = 0; i < n; i++) {
+		memcpy(elems[i].rot, inst[i].rotation, 36);
+		memcpy(elems[i].tr, inst[i].translation, 12);
+		instance_compute_bbox(elems[i], treeMin, treeMax);
+	}
+	std::vector<RefNode> nodes;
+	int depth = 0;
+	std::string err;
+	if(!build_dbvh(elems, nodes, depth, err)) {
+		set_error("%s", err.c_str());
+		return SNL_ERR_INVALID;
+	}
+	*nNodes = (int)nodes.size();
+	if(nodesOut)
+		memcpy(nodesOut, nodes.data(), nodes.size() * sizeof(RefNode));
+	for(int i = 0; i < n; i++) {
+		if(elementsOut) {
+			memcpy(elementsOut[i].rotation, elems[i].rot, 36);
+			memcpy(elementsOut[i].translation, elems[i].tr, 12);
+		}
+		if(bboxes6Out) {
+			memcpy(bboxes6Out + i * 6, elems[i].bmin, 12);
+			memcpy(bboxes6Out + i * 6 + 3, elems[i].bmax, 12);
+		}
+	}
+	return SNL_OK;
+}
+
+int snl_scene_copy_dbvh(snl_scene *s, int *nNodes, void *nodes, int *nInstances, snl_instance *elements, float *bboxes6) {
+	SNL_REQUIRE(s, SNL_ERR_INVALID, "null scene");
+	if(nNodes)
+		*nNodes = (int)s->topNodes.size();
+	if(nInstances)
+		*nInstances = (int)s->instances.size();
+	if(nodes)
+		memcpy(nodes, s->topNodes.data(), s->topNodes.size() * sizeof(RefNode));
+	for(size_t i = 0; i < s->instances.size(); i++) {
+		const HostInstance &e = s->instances[i];
+		if(elements) {
+			memcpy(elements[i].rotation, e.rot, 36);
+			memcpy(elements[i].translation, e.tr, 12);
+		}
+		if(bboxes6) {
+			memcpy(bboxes6 + i * 6, e.bmin, 12);
+			memcpy(bboxes6 + i * 6 + 3, e.bmax, 12);
+		}
+	}
+	return SNL_OK;
+}
+
 static int upload_materials(snl_scene *s, const snl_material *mats, int nMats, const snl_texture *tex, int nTex) {
 	SNL_CUDA(cudaSetDevice(s->device));
 	SNL_CUDA(cudaStreamSynchronize(s->stream));
@@ -644,7 +752,18 @@ extern "C" {
 			return r_;   \
 	} while(0)
 
+static int trace_primary_impl(snl_scene *s, const snl_camera *cam, int W, int H, int *instId, int *triId, float *t, float *bary2);
+
 int snl_trace_primary(snl_scene *s, const snl_camera *cam, int W, int H, int *triId, float *t, float *bary2) {
+	return trace_primary_impl(s, cam, W, H, nullptr, triId, t, bary2);
+}
+
+int snl_trace_primary_inst(snl_scene *s, const snl_camera *cam, int W, int H, int *instId, int *triId, float *t, float *bary2) {
+	SNL_REQUIRE(s && !s->instances.empty(), SNL_ERR_STATE, "no instances: call snl_scene_set_instances first");
+	return trace_primary_impl(s, cam, W, H, instId, triId, t, bary2);
+}
+
+static int trace_primary_impl(snl_scene *s, const snl_camera *cam, int W, int H, int *instId, int *triId, float *t, float *bary2) {
 	SNL_REQUIRE(s && cam && W > 0 && H > 0, SNL_ERR_INVALID, "bad argument");
 	SNL_TRY(begin_call(s));
 	const size_t n = (size_t)W * H;
@@ -658,9 +777,14 @@ int snl_trace_primary(snl_scene *s, const snl_camera *cam, int W, int H, int *tr
 	SNL_TRY(ensure_pre(s, s->originPre, cam->pos));
 	RayGenParams g;
 	make_raygen(*cam, W, H, g);
-	SNL_CUDA(launch_primary(S, s->originPre.set(), g, W, H, dId, dT, dB, s->stream));
+	int *dInst = nullptr;
+	if(instId)
+		SNL_TRY(scratch(s, 3, n, &dInst));
+	SNL_CUDA(launch_primary(S, s->originPre.set(), g, W, H, dId, dT, dB, dInst, s->stream));
 	s->launches++;
 	SNL_TRY(end_call(s));
+	if(instId)
+		SNL_CUDA(cudaMemcpyAsync(instId, dInst, n * 4, cudaMemcpyDeviceToHost, s->stream));
 	if(triId)
 		SNL_CUDA(cudaMemcpyAsync(triId, dId, n * 4, cudaMemcpyDeviceToHost, s->stream));
 	if(t)
@@ -689,6 +813,7 @@ static int upload_rays(snl_scene *s, const float *o3, const float *d3, const uns
 int snl_trace_rays(snl_scene *s, const float *o3, const float *d3, const unsigned char *mask, int n, int sharedOrigin,
 				   int *triId, float *t, float *bary2) {
 	SNL_REQUIRE(s && o3 && d3 && n >= 0, SNL_ERR_INVALID, "bad argument");
+	SNL_REQUIRE(s->instances.empty(), SNL_ERR_UNSUPPORTED, "snl_trace_rays is not available on an instanced scene (use snl_trace_primary_inst / snl_render)");
 	if(n == 0)
 		return SNL_OK;
 	SNL_TRY(begin_call(s));
@@ -718,6 +843,7 @@ int snl_trace_rays(snl_scene *s, const float *o3, const float *d3, const unsigne
 
 int snl_trace_shadow(snl_scene *s, const float origin[3], const float *d3, float *tmax_inout, int n) {
 	SNL_REQUIRE(s && origin && d3 && tmax_inout && n >= 0, SNL_ERR_INVALID, "bad argument");
+	SNL_REQUIRE(s->instances.empty(), SNL_ERR_UNSUPPORTED, "snl_trace_shadow is not available on an instanced scene (use snl_trace_primary_inst / snl_render)");
 	if(n == 0)
 		return SNL_OK;
 	SNL_TRY(begin_call(s));
@@ -739,6 +865,7 @@ int snl_trace_shadow(snl_scene *s, const float origin[3], const float *d3, float
 int snl_raytrace(snl_scene *s, const float *o3, const float *d3, const unsigned char *mask, int n, int sharedOrigin,
 				 float *rgb3, snl_stats *stats) {
 	SNL_REQUIRE(s && o3 && d3 && rgb3 && n >= 0, SNL_ERR_INVALID, "bad argument");
+	SNL_REQUIRE(s->instances.empty(), SNL_ERR_UNSUPPORTED, "snl_raytrace is not available on an instanced scene (use snl_trace_primary_inst / snl_render)");
 	if(n == 0)
 		return SNL_OK;
 	SNL_TRY(begin_call(s));
@@ -793,6 +920,7 @@ static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, cons
 						 size_t pitch, int rank) {
 	SceneDev S;
 	SNL_TRY(make_scene_dev(s, S));
+	SNL_REQUIRE(!(S.instances && S.gvSuper), SNL_ERR_UNSUPPORTED, "gVals[9] supersampling is not available on an instanced scene");
 	if(s->gVals[8]) {
 		S.gvTint = 1;
 		memcpy(S.tint, kRankTint[(unsigned)rank % 16], 12);
@@ -807,7 +935,7 @@ static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, cons
 		packets = s->dPackets.ptr;
 	}
 	const int nPk = packets ? s->nPackets : ((W + 15) / 16) * ((H + 15) / 16);
-	if(S.gvRefl && !S.gvDepth && !s->fused && !S.hasTransp && !S.gvSuper && nPk > 0) {
+	if(S.gvRefl && !S.gvDepth && !s->fused && !S.hasTransp && !S.gvSuper && !S.instances && nPk > 0) {
 		// reflection bounce: wavefront pipeline with queue-driven persistent traversal of the incoherent rays
 		const size_t NL = (size_t)nPk * kPacket, nl = std::max<size_t>(S.nLights, 1);
 		SNL_REQUIRE(NL * nl < 0xffffffffull, SNL_ERR_UNSUPPORTED, "frame too large for 32-bit ray ids");
@@ -855,7 +983,7 @@ static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, cons
 		const char *pin = getenv("SNL_RENDER_VARIANT");
 		if(pin && (pin[0] == '0' || pin[0] == '1'))
 			T.choice = pin[0] - '0';
-		else if(S.hasTransp || S.gvSuper || nPk < 4 * s->smCount)
+		else if(S.hasTransp || S.gvSuper || S.instances || nPk < 4 * s->smCount)
 			T.choice = 0;  // only the plain kernel has the second variant; tiny frames are not worth tuning
 	}
 	if(T.choice < 0) {

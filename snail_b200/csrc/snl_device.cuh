@@ -95,6 +95,7 @@ struct Hit {
 	float dist;
 	int obj;
 	float bu, bv;
+	int inst;  // instanced scenes only: Context::object (index into DBVH::elements); obj is then Context::element
 };
 
 // Triangle::Collide(Context<1,*>&) per ray (src/triangle.cpp:3-63), sharedOrigin form with the per-origin
@@ -120,6 +121,10 @@ __device__ __forceinline__ void tri_nearest_pre(const PreTri *__restrict__ t, in
 }
 
 // Triangle::Collide(Context<0,*>&) per ray (src/triangle.cpp:29-37,41-61): per-ray origin.
+// SHORDER: the sharedOrigin form's operation order (tvec0 / tvec1 scaled by it0 BEFORE the dot products, :13-18) on an
+// origin that is not known per frame: a shared origin seen from inside an instance (ObjectInstance::CollidePrimary
+// hands BVH::TraversePrimary a Context<1,*>, src/dbvh/tree.h:118-165).
+template <bool SHORDER = false>
 __device__ __forceinline__ void tri_nearest_gen(const GenTri *__restrict__ t, int idx, float ox, float oy, float oz,
 												float dx, float dy, float dz, Hit &h) {
 	float4 ta, tba, tca, tn;
@@ -131,8 +136,8 @@ __device__ __forceinline__ void tri_nearest_gen(const GenTri *__restrict__ t, in
 	const float t0x = tba.y * tz - tba.z * ty, t0y = tba.z * tx - tba.x * tz, t0z = tba.x * ty - tba.y * tx;
 	const float t1x = ty * tca.z - tz * tca.y, t1y = tz * tca.x - tx * tca.z, t1z = tx * tca.y - ty * tca.x;
 	const float tmul = -(tx * tn.x + ty * tn.y + tz * tn.z);
-	const float v = (dx * t0x + dy * t0y + dz * t0z) * ta.w;
-	const float u = (dx * t1x + dy * t1y + dz * t1z) * ta.w;
+	const float v = SHORDER ? dx * (t0x * ta.w) + dy * (t0y * ta.w) + dz * (t0z * ta.w) : (dx * t0x + dy * t0y + dz * t0z) * ta.w;
+	const float u = SHORDER ? dx * (t1x * ta.w) + dy * (t1y * ta.w) + dz * (t1z * ta.w) : (dx * t1x + dy * t1y + dz * t1z) * ta.w;
 	const float duv = det - u - v;
 	const float uvmin = fminf(u, fminf(v, duv));
 	const float uvmax = fmaxf(u, fmaxf(v, duv));
@@ -250,7 +255,7 @@ __device__ __forceinline__ void node_test(const GpuNode *__restrict__ n, float o
 }
 
 // BVH::TraversePrimaryN per ray (src/bvh/traverse.cpp:14-80).
-template <bool SHARED>
+template <bool SHARED, bool SHORDER = false>
 __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nodes, const void *__restrict__ tris,
 												 float ox, float oy, float oz, float dx, float dy, float dz, float ix,
 												 float iy, float iz, Hit &h, TravCount &tc) {
@@ -285,7 +290,7 @@ __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nod
 				}
 				else {
 					SNL_COUNT(tc.gtris);
-					tri_nearest_gen(reinterpret_cast<const GenTri *>(tris) + first + i, first + i, ox, oy, oz, dx, dy, dz, h);
+					tri_nearest_gen<SHORDER>(reinterpret_cast<const GenTri *>(tris) + first + i, first + i, ox, oy, oz, dx, dy, dz, h);
 				}
 			}
 			leaf = cur;
@@ -297,8 +302,10 @@ __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nod
 
 // BVH::TraverseShadow per ray (src/bvh/traverse.cpp:82-149) with Triangle::Collide(ShadowContext&)
 // (src/triangle.cpp:65-102): any hit, ONE-SIDED (only triangles with dir.nrm >= u+v >= 0 occlude), no division.
-// Origin = light position: nodes are that light's translated boxes, triangles its PreTri records.
-__device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ nodes, const PreTri *__restrict__ tris, float ox,
+// Origin = light position; triangles = that light's PreTri records, or (GEN, instanced scenes: the light seen from
+// inside an instance) the GenTri records with the sharedOrigin precomputation (src/triangle.cpp:13-18) done on the fly.
+template <bool GEN = false>
+__device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ nodes, const void *__restrict__ tris, float ox,
 												float oy, float oz, float dx, float dy, float dz, float ix, float iy, float iz,
 												float dist, TravCount &tc) {
 #ifndef SNL_BOX_EXACT
@@ -326,8 +333,24 @@ __device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ node
 			const int first = lf & kLeafFirstMask, count = (lf >> kLeafFirstBits) + 1;
 			for(int i = 0; i < count; i++) {
 				SNL_COUNT(tc.tris);
-				const PreTri *t = tris + first + i;
-				const float4 tu = ldg4(&t->u), tv = ldg4(&t->v), tn = ldg4(&t->n);
+				float4 tu, tv, tn;
+				if(GEN) {
+					const GenTri *t = reinterpret_cast<const GenTri *>(tris) + first + i;
+					float4 ta, tba, tca;
+					ldg8(&t->a, ta, tba);
+					ldg8(&t->ca, tca, tn);
+					const float tx = ox - ta.x, ty = oy - ta.y, tz = oz - ta.z;
+					tv = make_float4((tba.y * tz - tba.z * ty) * ta.w, (tba.z * tx - tba.x * tz) * ta.w,
+									 (tba.x * ty - tba.y * tx) * ta.w, 0.0f);
+					tu = make_float4((ty * tca.z - tz * tca.y) * ta.w, (tz * tca.x - tx * tca.z) * ta.w,
+									 (tx * tca.y - ty * tca.x) * ta.w, -(tx * tn.x + ty * tn.y + tz * tn.z));
+				}
+				else {
+					const PreTri *t = reinterpret_cast<const PreTri *>(tris) + first + i;
+					tu = ldg4(&t->u);
+					tv = ldg4(&t->v);
+					tn = ldg4(&t->n);
+				}
 				const float det = dx * tn.x + dy * tn.y + dz * tn.z;
 				const float v = dx * tv.x + dy * tv.y + dz * tv.z;
 				const float u = dx * tu.x + dy * tu.y + dz * tu.z;
@@ -349,6 +372,109 @@ __device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ node
 
 // SafeInv (src/rtbase.h:117-119): Inv(v + 1e-8).
 __device__ __forceinline__ float safe_inv(float v) { return 1.0f / (v + 0.00000001f); }
+
+// ---- instanced two-level BVH (DBVH, src/dbvh/tree.h, src/dbvh/traverse.cpp) ----------------------------------------
+// Top level: a tree over the instances in the same GpuNode layout (leaf link = a range of DBVH::elements). An instance
+// is entered by transforming the ray into its space (ObjectInstance::ITransformVec / ITransformPoint,
+// src/dbvh/tree.h:32-44; the rotation is orthonormal, so t is shared) and walking the ONE bottom-level BVH there with
+// the shared hit record, exactly what CollidePrimary / CollideShadow do per packet.
+enum { kTopStack = 66 };  // DBVH::maxDepth + 2
+
+__device__ __forceinline__ void inst_ray(const DevInstance *__restrict__ I, float ox, float oy, float oz, float dx, float dy,
+										 float dz, float &lox, float &loy, float &loz, float &ldx, float &ldy, float &ldz) {
+	float4 r0, r1, r2, t;
+	ldg8(&I->r0, r0, r1);
+	ldg8(&I->r2, r2, t);
+	ldx = dx * r0.x + dy * r1.x + dz * r2.x;  // ITransformVec
+	ldy = dx * r0.y + dy * r1.y + dz * r2.y;
+	ldz = dx * r0.z + dy * r1.z + dz * r2.z;
+	const float px = ox - t.x, py = oy - t.y, pz = oz - t.z;  // ITransformPoint: p -= translation first
+	lox = px * r0.x + py * r1.x + pz * r2.x;
+	loy = px * r0.y + py * r1.y + pz * r2.y;
+	loz = px * r0.z + py * r1.z + pz * r2.z;
+}
+
+// DBVH::TraversePrimary0 per ray. SHARED: the rays of the launch share their origin (the reference then uses the
+// sharedOrigin triangle arithmetic inside the instances).
+template <bool SHARED>
+__device__ __forceinline__ void traverse_nearest_inst(const SceneDev &S, float ox, float oy, float oz, float dx, float dy,
+													  float dz, float ix, float iy, float iz, Hit &h, TravCount &tc) {
+	int stack[kTopStack];
+	int sp = 0;
+	stack[sp++] = kSentinel;
+	int cur = 0;
+	const float bx = ox * ix, by = oy * iy, bz = oz * iz;
+	while(cur != kSentinel) {
+		if(cur >= 0) {
+			bool h0, h1;
+			float lmin0, lmin1;
+			int l0, l1;
+			node_test<false>(S.topNodes + cur, bx, by, bz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
+			const bool swap = lmin1 < lmin0;
+			if(h0 && h1) {
+				stack[sp++] = swap ? l0 : l1;
+				cur = swap ? l1 : l0;
+			}
+			else if(h0 || h1)
+				cur = h0 ? l0 : l1;
+			else
+				cur = stack[--sp];
+		}
+		else {
+			const int lf = ~cur;
+			const int first = lf & kLeafFirstMask, count = (lf >> kLeafFirstBits) + 1;
+			for(int i = 0; i < count; i++) {
+				float lox, loy, loz, ldx, ldy, ldz;
+				inst_ray(S.instances + first + i, ox, oy, oz, dx, dy, dz, lox, loy, loz, ldx, ldy, ldz);
+				const float before = h.dist;
+				traverse_nearest<false, SHARED>(S.nodes, S.gtris, lox, loy, loz, ldx, ldy, ldz, safe_inv(ldx), safe_inv(ldy),
+												safe_inv(ldz), h, tc);
+				if(h.dist < before)
+					h.inst = first + i;
+			}
+			cur = stack[--sp];
+		}
+	}
+}
+
+// DBVH::TraverseShadow0 per ray: any hit inside any instance; the shadow rays of a light share their origin.
+__device__ __forceinline__ bool traverse_shadow_inst(const SceneDev &S, float ox, float oy, float oz, float dx, float dy, float dz,
+													 float ix, float iy, float iz, float dist, TravCount &tc) {
+	int stack[kTopStack];
+	int sp = 0;
+	stack[sp++] = kSentinel;
+	int cur = 0;
+	const float bx = ox * ix, by = oy * iy, bz = oz * iz;
+	while(cur != kSentinel) {
+		if(cur >= 0) {
+			bool h0, h1;
+			float lmin0, lmin1;
+			int l0, l1;
+			node_test<false>(S.topNodes + cur, bx, by, bz, ix, iy, iz, dist, h0, h1, lmin0, lmin1, l0, l1);
+			if(h0 && h1) {
+				stack[sp++] = l1;
+				cur = l0;
+			}
+			else if(h0 || h1)
+				cur = h0 ? l0 : l1;
+			else
+				cur = stack[--sp];
+		}
+		else {
+			const int lf = ~cur;
+			const int first = lf & kLeafFirstMask, count = (lf >> kLeafFirstBits) + 1;
+			for(int i = 0; i < count; i++) {
+				float lox, loy, loz, ldx, ldy, ldz;
+				inst_ray(S.instances + first + i, ox, oy, oz, dx, dy, dz, lox, loy, loz, ldx, ldy, ldz);
+				if(traverse_shadow<true>(S.nodes, S.gtris, lox, loy, loz, ldx, ldy, ldz, safe_inv(ldx), safe_inv(ldy),
+										 safe_inv(ldz), dist, tc))
+					return true;
+			}
+			cur = stack[--sp];
+		}
+	}
+	return false;
+}
 
 // RayGenerator::Generate (src/ray_generator.cpp:23-47) for thread (tx, ty) of the 16x16 packet at (x0, y0).
 __device__ __forceinline__ void gen_primary(const RayGenParams &g, int x0, int y0, int tx, int ty, float &dx, float &dy,
@@ -497,7 +623,9 @@ __device__ __forceinline__ void material_shade(const SceneDev &S, int matId, boo
 // TRANSP: also evaluates transSel for the lane (`trans`): the material has fTransparency and, in a block shaded per
 // material, it is the LAST such material in order of first appearance - `transSel[b4 + q] = mask[q]` overwrites the
 // whole block for every transparent material in turn (src/scene_trace.cpp:190,306,347-349).
-template <bool TRANSP>
+// INST: instanced scene. DBVH::HasShadingData() is 0 (src/dbvh/tree.h:204-206), so shading is always the simple path,
+// with the geometric normal rotated into world space (ObjectInstance::GetNormal, :171-174).
+template <bool TRANSP, bool INST = false>
 __device__ __forceinline__ void shade_block(const SceneDev &S, bool sel, const Hit &h, float ox, float oy, float oz, float dx,
 											float dy, float dz, bool packetHasMask, Sample &s, bool &trans) {
 	const int lane = threadIdx.x & 31;
@@ -518,7 +646,7 @@ __device__ __forceinline__ void shade_block(const SceneDev &S, bool sel, const H
 	const bool blockFull = selB == 0xffffu;
 	const bool fast = blockFull && sameB == 0xffffu;
 
-	if(S.gvFull && S.shtris) {
+	if(!INST && S.gvFull && S.shtris) {
 		int matId = -1;
 		float tu = 0.0f, tv = 0.0f;
 		bool texCoords = false;
@@ -583,9 +711,18 @@ __device__ __forceinline__ void shade_block(const SceneDev &S, bool sel, const H
 	else if(sel) {
 		// simple shading: geometric normal, default material (src/scene_trace.cpp:359-452)
 		const float4 tn = ldg4(&S.gtris[obj].n);
-		s.nx = tn.x;
-		s.ny = tn.y;
-		s.nz = tn.z;
+		if(INST) {  // TransformVec: rotation rows dotted with the normal
+			const DevInstance *I = S.instances + h.inst;
+			const float4 r0 = ldg4(&I->r0), r1 = ldg4(&I->r1), r2 = ldg4(&I->r2);
+			s.nx = tn.x * r0.x + tn.y * r0.y + tn.z * r0.z;
+			s.ny = tn.x * r1.x + tn.y * r1.y + tn.z * r1.z;
+			s.nz = tn.x * r2.x + tn.y * r2.y + tn.z * r2.z;
+		}
+		else {
+			s.nx = tn.x;
+			s.ny = tn.y;
+			s.nz = tn.z;
+		}
 		material_shade(S, -1, false, dx, dy, dz, 0.0f, 0.0f, 0.0f, 0.0f, s);
 	}
 }
@@ -632,6 +769,7 @@ __device__ __forceinline__ void light_accumulate(const DevLight &L, float dot, f
 }
 
 // Returns true when a shadow ray was cast.
+template <bool INST = false>
 __device__ __forceinline__ bool trace_light(const SceneDev &S, int li, bool sel, const Sample &s, float &ldr, float &ldg,
 											float &ldb, float &lsr, float &lsg, float &lsb, TravCount &tc) {
 	if(!sel)
@@ -641,8 +779,10 @@ __device__ __forceinline__ bool trace_light(const SceneDev &S, int li, bool sel,
 	if(!light_setup(L, s.px, s.py, s.pz, s.nx, s.ny, s.nz, fx, fy, fz, dot, distance))
 		return false;
 	const float tmax = distance * 0.9999f;
-	const bool occluded = traverse_shadow(kRelNodes ? S.lightPre[li].nodes : S.nodes, S.lightPre[li].tris, L.pos[0], L.pos[1],
-										  L.pos[2], fx, fy, fz, safe_inv(fx), safe_inv(fy), safe_inv(fz), tmax, tc);
+	const bool occluded =
+		INST ? traverse_shadow_inst(S, L.pos[0], L.pos[1], L.pos[2], fx, fy, fz, safe_inv(fx), safe_inv(fy), safe_inv(fz), tmax, tc)
+			 : traverse_shadow(kRelNodes ? S.lightPre[li].nodes : S.nodes, S.lightPre[li].tris, L.pos[0], L.pos[1], L.pos[2], fx,
+							   fy, fz, safe_inv(fx), safe_inv(fy), safe_inv(fz), tmax, tc);
 	if(!occluded && tmax > 0.0f)
 		light_accumulate(L, dot, distance, ldr, ldg, ldb, lsr, lsg, lsb);
 	return true;
@@ -736,7 +876,7 @@ __device__ __forceinline__ void level_compose(const SceneDev &S, const LevelOut 
 
 enum { kMaxTransp = 8 };  // transparent surfaces followed along one ray (the reference recursion has no cap)
 
-template <int LEVEL, bool SHARED, bool TRANSP>
+template <int LEVEL, bool SHARED, int FLAGS>
 __device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet originPre, bool active, int maskGen,
 											  float ox, float oy, float oz, float dx, float dy, float dz, float &outr,
 											  float &outg, float &outb, PacketCounts &pc, TravCount &tc);
@@ -745,17 +885,22 @@ __device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet or
 // transparency pass: nearest hit, Sample + material, reflection bounce (LEVEL 0), lights. Returns true when the lane
 // is in transSel with opacity < 1 (:468-472); `hitDist` is its tDistance. DEPTH0: the rays are the level's own
 // (else: a transparency continuation, counted as such). All 256 threads of the CTA must call it.
-template <int LEVEL, bool SHARED, bool TRANSP, bool DEPTH0>
+template <int LEVEL, bool SHARED, int FLAGS, bool DEPTH0>
 __device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet originPre, bool active, int maskGen,
 											   float ox, float oy, float oz, float dx, float dy, float dz, LevelOut &f,
 											   float &hitDist, bool &depthOnly, PacketCounts &pc, TravCount &tc) {
+	// FLAGS: 1 = the scene can start transparency passes, 2 = instanced scene (DBVH)
+	constexpr bool TRANSP = (FLAGS & 1) != 0, INST = (FLAGS & 2) != 0;
 	Hit h;
 	h.dist = CUDART_INF_F;
 	h.obj = 0;
+	h.inst = 0;
 	h.bu = h.bv = 0.0f;
 	if(active) {
 		const float ix = safe_inv(dx), iy = safe_inv(dy), iz = safe_inv(dz);
-		if(SHARED)
+		if(INST)
+			traverse_nearest_inst<SHARED>(S, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
+		else if(SHARED)
 			traverse_nearest<true>(kRelNodes ? originPre.nodes : S.nodes, originPre.tris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
 		else
 			traverse_nearest<false>(S.nodes, S.gtris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
@@ -785,7 +930,7 @@ __device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet o
 	bool trans;
 	// maskGen > 0: "ask packet vote maskGen" (posted by the level above before this level's traversal)
 	const bool packetHasMask = maskGen > 0 ? !packet_vote_all(maskGen) : maskGen != 0;
-	shade_block<TRANSP>(S, sel, h, ox, oy, oz, dx, dy, dz, packetHasMask, s, trans);
+	shade_block<TRANSP, INST>(S, sel, h, ox, oy, oz, dx, dy, dz, packetHasMask, s, trans);
 
 	if(LEVEL == 0 && S.gvRefl) {  // src/scene_trace.cpp:454-466, TraceReflection :603-618
 		// selector.All() of the packet (src/scene_trace.cpp:615-617) picks RayGroup<0,0> or <0,1> for the bounce; only
@@ -794,7 +939,7 @@ __device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet o
 		float rx, ry, rz, rox, roy, roz;
 		reflection_ray(s, dx, dy, dz, rx, ry, rz, rox, roy, roz);
 		float cr = 0.0f, cg = 0.0f, cb = 0.0f;
-		raytrace_lane<1, false, TRANSP>(S, PreSet{nullptr, nullptr}, sel, refMask, rox, roy, roz, rx, ry, rz, cr, cg, cb, pc, tc);
+		raytrace_lane<1, false, FLAGS>(S, PreSet{nullptr, nullptr}, sel, refMask, rox, roy, roz, rx, ry, rz, cr, cg, cb, pc, tc);
 		if(sel) {
 			s.dr = s.dr + (cr - s.dr) * 0.3f;
 			s.dg = s.dg + (cg - s.dg) * 0.3f;
@@ -810,7 +955,7 @@ __device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet o
 		float ldr = S.ambient[0], ldg = S.ambient[1], ldb = S.ambient[2];
 		float lsr = 0.0f, lsg = 0.0f, lsb = 0.0f;
 		for(int li = 0; li < S.nLights; li++) {
-			const bool cast = trace_light(S, li, sel, s, ldr, ldg, ldb, lsr, lsg, lsb, tc);
+			const bool cast = trace_light<INST>(S, li, sel, s, ldr, ldg, ldb, lsr, lsg, lsb, tc);
 			if(cast) {
 				if(LEVEL == 0)
 					pc.shadow++;
@@ -835,14 +980,15 @@ __device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet o
 // dir * (t + 0.001) + origin and lerps the result into diffuse BEFORE the lights are applied; lights and the bounce do
 // not depend on that result, so the recursion is unrolled into a loop that keeps one LevelOut per surface and composes
 // the colours back to front afterwards with the reference's expression order. All 256 threads must call it.
-template <int LEVEL, bool SHARED, bool TRANSP>
+template <int LEVEL, bool SHARED, int FLAGS>
 __device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet originPre, bool active, int maskGen,
 											  float ox, float oy, float oz, float dx, float dy, float dz, float &outr,
 											  float &outg, float &outb, PacketCounts &pc, TravCount &tc) {
 	LevelOut f;
 	float hitDist;
 	bool depthOnly;
-	bool cont = raytrace_level<LEVEL, SHARED, TRANSP, true>(S, originPre, active, maskGen, ox, oy, oz, dx, dy, dz, f,
+	constexpr bool TRANSP = (FLAGS & 1) != 0;
+	bool cont = raytrace_level<LEVEL, SHARED, FLAGS, true>(S, originPre, active, maskGen, ox, oy, oz, dx, dy, dz, f,
 															hitDist, depthOnly, pc, tc);
 	if(depthOnly) {
 		outr = f.ar;
@@ -869,7 +1015,7 @@ __device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet or
 			// every lane takes part (shading blocks are warp-wide); only continued lanes take the new level's result
 			LevelOut nf;
 			float nDist;
-			const bool more = raytrace_level<LEVEL, false, TRANSP, false>(S, PreSet{nullptr, nullptr}, cont, n != kPacket ? -1 : 0, ox,
+			const bool more = raytrace_level<LEVEL, false, FLAGS, false>(S, PreSet{nullptr, nullptr}, cont, n != kPacket ? -1 : 0, ox,
 																		  oy, oz, dx, dy, dz, nf, nDist, depthOnly, pc, tc);
 			if(cont) {
 				f = nf;

@@ -44,6 +44,17 @@ struct HostScene {
 enum { kNoShadingData = 1, kFastBuild = 2, kUseSah = 4 };  // src/bvh/tree.h:21-25
 enum { kDeviceBuild = 8 };  // ours: leave HostBVH::nodes empty, the tree is built on the GPU (snl_build.cu)
 
+// ObjectInstance (src/dbvh/tree.h:7-187): rotation rows, translation, world box.
+struct HostInstance {
+	float rot[3][3];
+	float tr[3];
+	float bmin[3], bmax[3];
+};
+// ObjectInstance::ComputeBBox + DBVH::Construct (src/dbvh/tree.cpp:4-21,159-173), snl_host_dbvh.cpp. build_dbvh reorders
+// `elems` exactly as the reference's std::partition does and emits DBVH::Node records (same 32-byte layout as BVH::Node).
+void instance_compute_bbox(HostInstance &inst, const float treeMin[3], const float treeMax[3]);
+bool build_dbvh(std::vector<HostInstance> &elems, std::vector<RefNode> &nodes, int &depth, std::string &err);
+
 // Returns false and fills err on failure.
 bool load_obj_scene(const char *objPath, const char *mtlPath, const char *texDir, int flipNormalsFlag, int buildFlags,
 					HostScene &out, std::string &err);

@@ -45,9 +45,10 @@ __global__ void __launch_bounds__(256) k_pretransform(const GenTri *__restrict__
 
 // ---- BVH::TraversePrimary on generated primary rays (snl_trace_primary) -------------------------------------
 // grid = packets (16x16 pixels), block = 256.
+template <bool INST>
 __global__ void __launch_bounds__(kPacket) k_primary(SceneDev S, const PreSet pre, RayGenParams g, int W, int H,
 												  int packetsX, int *__restrict__ triId, float *__restrict__ t,
-												  float *__restrict__ bary) {
+												  float *__restrict__ bary, int *__restrict__ instId) {
 	const int px0 = (blockIdx.x % packetsX) * 16, py0 = (blockIdx.x / packetsX) * 16;
 	const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
 	const int x = px0 + tx, y = py0 + ty;
@@ -60,14 +61,21 @@ __global__ void __launch_bounds__(kPacket) k_primary(SceneDev S, const PreSet pr
 		Hit h;
 		h.dist = CUDART_INF_F;
 		h.obj = 0;
+		h.inst = 0;
 		h.bu = h.bv = 0.0f;
-		traverse_nearest<true>(kRelNodes ? pre.nodes : S.nodes, pre.tris, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, safe_inv(dx), safe_inv(dy),
-							   safe_inv(dz), h, tc);
+		if(INST)  // DBVH::TraversePrimary(Context<1,0>&)
+			traverse_nearest_inst<true>(S, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, safe_inv(dx), safe_inv(dy),
+										safe_inv(dz), h, tc);
+		else
+			traverse_nearest<true>(kRelNodes ? pre.nodes : S.nodes, pre.tris, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz,
+								   safe_inv(dx), safe_inv(dy), safe_inv(dz), h, tc);
 		pc.primary = 1;
 		const size_t o = (size_t)y * W + x;
 		const bool hit = h.dist < CUDART_INF_F;
 		if(triId)
 			triId[o] = hit ? h.obj : -1;
+		if(INST && instId)
+			instId[o] = hit ? h.inst : -1;
 		if(t)
 			t[o] = h.dist;
 		if(bary) {
@@ -177,12 +185,12 @@ __device__ __forceinline__ unsigned conv_channel(float c) {
 #ifndef SNL_RENDER_MIN_BLOCKS
 #define SNL_RENDER_MIN_BLOCKS 4
 #endif
-// TRANSP: the scene has a material that can start a transparency pass. SUPER: gVals[9], every 16x16 output packet is
+// FLAGS: 1 = the scene has a material that can start a transparency pass, 2 = instanced scene (DBVH). SUPER: gVals[9], every 16x16 output packet is
 // traced as four 16x16 packets of the 2W x 2H image and box-filtered (src/render.cpp:71-110).
 // MINB: resident CTAs per SM the register allocation aims for. 4 (64 registers) suits scenes whose hot set sits in L1;
 // 5 (48 registers, a few more spills) hides more latency on large scenes: +1.9 % on sponza_like, -2 % on feline.
 // The scene picks per workload by timing both on its first frames (snl_capi.cu render_common).
-template <bool TRANSP, bool SUPER, int MINB>
+template <int FLAGS, bool SUPER, int MINB>
 __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreSet pre, RayGenParams g, int W, int H,
 												 int packetsX, const int4 *__restrict__ packets,
 												 unsigned char *__restrict__ out, size_t pitch) {
@@ -216,7 +224,7 @@ __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreS
 		else
 			gen_primary(g, px0, py0, tx, ty, dx, dy, dz);
 		float r = 0.0f, gg = 0.0f, b = 0.0f;
-		raytrace_lane<0, true, TRANSP>(S, pre, active, 0, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, r, gg, b, pc, tc);
+		raytrace_lane<0, true, FLAGS>(S, pre, active, 0, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, r, gg, b, pc, tc);
 		int ox = tx, oy = ty;
 		bool store = true;
 		if(SUPER) {
@@ -266,9 +274,12 @@ cudaError_t launch_pretransform(const GenTri *gtris, int nTris, const GpuNode *n
 }
 
 cudaError_t launch_primary(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, int *triId, float *t,
-						   float *bary, cudaStream_t st) {
+						   float *bary, int *instId, cudaStream_t st) {
 	const int px = (W + 15) / 16, py = (H + 15) / 16;
-	k_primary<<<px * py, kPacket, 0, st>>>(S, pre, g, W, H, px, triId, t, bary);
+	if(S.instances)
+		k_primary<true><<<px * py, kPacket, 0, st>>>(S, pre, g, W, H, px, triId, t, bary, instId);
+	else
+		k_primary<false><<<px * py, kPacket, 0, st>>>(S, pre, g, W, H, px, triId, t, bary, instId);
 	return cudaGetLastError();
 }
 
@@ -317,18 +328,20 @@ cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenPara
 	if(grid <= 0)
 		return cudaSuccess;
 	const int MB = SNL_RENDER_MIN_BLOCKS;
-	if(S.hasTransp) {
+	if(S.instances)  // Scene<DBVH>: simple shading only, so no transparency; supersampling is refused by the caller
+		k_render<2, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+	else if(S.hasTransp) {
 		if(S.gvSuper)
-			k_render<true, true, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+			k_render<1, true, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
 		else
-			k_render<true, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+			k_render<1, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
 	}
 	else if(S.gvSuper)
-		k_render<false, true, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+		k_render<0, true, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
 	else if(variant == 1)
-		k_render<false, false, MB + 1><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+		k_render<0, false, MB + 1><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
 	else
-		k_render<false, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+		k_render<0, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
 	return cudaGetLastError();
 }
 

@@ -74,6 +74,13 @@ struct snl_scene {
 	float devBBox[6] = {0};    // its scene box
 	float buildMs = 0.0f;      // device time of the last device build
 
+	// instanced form (DBVH over ObjectInstances of this scene's BVH, snl_scene_set_instances); empty = plain BVH
+	std::vector<snl::HostInstance> instances;  // in DBVH::elements order
+	std::vector<snl::RefNode> topNodes;        // DBVH::nodes
+	int topDepth = 0;
+	snl::DevBuf<snl::GpuNode> dTopNodes;
+	snl::DevBuf<snl::DevInstance> dInstances;
+
 	snl::DevBuf<snl::GpuNode> dNodes;
 	snl::DevBuf<snl::GenTri> dTris;
 	snl::DevBuf<snl::RefShTri> dShTris;

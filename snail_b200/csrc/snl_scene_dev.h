@@ -21,6 +21,8 @@ struct SceneDev {
 	const int *triMat;       // BVH::materials[i].id
 	const DevMaterial *mats;
 	const DevTexture *texs;
+	const GpuNode *topNodes;      // instanced scene (DBVH): top-level tree over the instances, leaves = instance ranges
+	const DevInstance *instances; // in DBVH::elements order; null = plain BVH
 	PreSet lightPre[kMaxLights];
 	DevLight lights[kMaxLights];
 	int nTriMat, nMats, nLights;

@@ -83,6 +83,12 @@ struct SNL_ALIGN16 PreTri {
 };
 static_assert(sizeof(PreTri) == 48, "PreTri is 48 bytes");
 
+// ObjectInstance on the device: rotation rows + translation (src/dbvh/tree.h:177-178), 64 B.
+struct SNL_ALIGN16 DevInstance {
+	Float4 r0, r1, r2;  // rotation[0..2].xyz
+	Float4 t;           // translation.xyz
+};
+
 struct DevMaterial {
 	int32_t kind, flags;
 	float color[3];

@@ -68,6 +68,68 @@ def random_rays(n, bmin, bmax, seed):
     return o, d.astype(np.float32)
 
 
+def make_instances(n, scale, seed=1):
+    """Instances in the spirit of MakeDBVH (src/rtracer.cpp:146-178): n random rotations + translations on a grid of
+    `scale`, plus the identity instance. Returns (n + 1, 12) float32 {rotation rows, translation}."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for _ in range(n):
+        a = rng.random(3) * 2 * np.pi
+        (cx, cy, cz), (sx, sy, sz) = np.cos(a), np.sin(a)
+        rx = np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]])
+        ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+        rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]])
+        rot = (rz @ ry @ rx).astype(np.float32)
+        tr = ((rng.integers(0, 1000, 3) - 500) * scale).astype(np.float32)
+        out.append(np.concatenate([rot.reshape(-1), tr]))
+    out.append(np.float32([1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0]))
+    return np.array(out, np.float32)
+
+
+INST_STAGES = {"simple_nolight": ({}, False), "depth": ({1: 1}, False), "simple_light": ({}, True),
+               "refl_nolight": ({7: 1}, False),
+               "whitted": ({7: 1}, True)}  # Scene<DBVH> has no shading data: gVals[6] changes nothing
+# name -> (obj, instances besides the identity, W, H)
+INST_CASES = {"lancia_inst": ("lancia.obj", 60, 160, 96), "box_inst": ("box.obj", 24, 128, 80)}
+
+
+def instanced_cases(manifest):
+    """Scene<DBVH> (src/dbvh/tree.h): top-level tree + instance order, per-pixel {instance, triangle, t, bary} of
+    DBVH::TraversePrimary, frames per stage."""
+    for name, (obj, n, W, H) in INST_CASES.items():
+        ref = R.RefScene(os.path.join(SCENES, obj), variant="scalar")
+        bmin, bmax = ref.bbox()
+        S = float(np.linalg.norm(bmax - bmin))
+        inst = make_instances(n, S * 0.004, seed=len(name))
+        ref.set_instances(inst)
+        nodes, elems, boxes = ref.dbvh()
+        c = (bmin + bmax) * 0.5
+        cam = R.camera_array(c - np.float32([0.07, 0.11, 1]) * np.float32(3.5 * S))
+        light = np.array([*cam[:3], 1, 1, 1, 12 * S], np.float32)
+        out = {"instances": inst, "camera": cam, "light": light, "size": np.array([W, H], np.int32),
+               "dbvh_elements": elems, "dbvh_boxes": boxes}
+        ref.set_gvals({})
+        ref.set_lights([])
+        out["inst"], out["tri"], out["t"], out["bary"] = ref.trace_primary_inst(cam, W, H)
+        # same uninitialised-normal quirk as in BVH scenes, here for (instance 0, triangle 0) (src/scene_trace.cpp:410-423)
+        lane0 = np.repeat(out["inst"][:, 0::4], 4, axis=1)[:, :W]
+        out["undef_simple"] = (out["inst"] == 0) & (out["tri"] == 0) & (lane0 < 0)
+        rays = {}
+        for stage, (gv, lit) in INST_STAGES.items():
+            ref.set_gvals(gv)
+            ref.set_lights([light] if lit else [])
+            img, st, _ = ref.render(cam, W, H, threads=1)
+            out["img_" + stage] = img
+            rays[stage] = st["rays"]
+        np.savez_compressed(os.path.join(GOLDEN, name + ".npz"), **out)
+        manifest["instanced"][name] = {"obj": obj, "W": W, "H": H, "n_instances": int(len(inst)), "n_nodes": int(len(nodes)),
+                                       "sha256_dbvh_nodes": sha(nodes), "rays": rays,
+                                       "hits": int((out["inst"] >= 0).sum()),
+                                       "instances_hit": int(len(np.unique(out["inst"][out["inst"] >= 0])))}
+        print(name, manifest["instanced"][name])
+        ref.close()
+
+
 def sha(a: np.ndarray) -> str:
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
 
@@ -152,6 +214,8 @@ def main():
         }
         print(name, manifest["cases"][name]["hits"], "hits of", W * H, "rays:", rays)
         ref.close()
+    manifest["instanced"] = {}
+    instanced_cases(manifest)
     with open(os.path.join(GOLDEN, "manifest.json"), "w") as f:
         json.dump(manifest, f, indent=1, sort_keys=True)
 
