@@ -221,6 +221,16 @@ int snl_render_dev(snl_scene *, const snl_camera *cam, int W, int H, const int *
 				   void *bgr8_dev, size_t pitch, int rank);
 int snl_scene_sync(snl_scene *, snl_stats *stats);
 
+/* The farm overload of Render() with its wire format (src/render.h:20-23, src/render.cpp:243-265, RenderTask with
+ * compress == 1, src/render.cpp:140-166): tile i = coords[4i..4i+3] = {x, y, w, h} is written at data + offsets[i] as
+ * three w*h byte planes - colour.x, colour.y - colour.x, colour.z - colour.x (mod 256, what DecompressTask of
+ * src/compression.cpp:132-139 undoes) - w bytes per row. The reference only writes tiles of exactly 16 x 64 (its
+ * maxWidth x maxHeight; others hit a TODO and stay unwritten); here any tile with x, w multiples of 16 is written in the
+ * same layout. data is a host buffer of at least max(offsets[i] + 3*w*h) bytes; bytes between tiles are untouched.
+ * rank feeds the gVals[8] tint like the reference's. The header / QuickLZ framing of src/node.cpp is not part of this. */
+int snl_render_farm(snl_scene *, const snl_camera *cam, int resx, int resy, unsigned char *data, const int *coords,
+					const int *offsets, int nTiles, int rank, snl_stats *stats);
+
 /* Multi-GPU compose over NVLink peer memory (replaces the tile transport of src/node.cpp:20-120 / src/comm_mpi.cpp and
  * the per-tile receive loop of src/server.cpp:330-418). Rank 0 creates the frame on its device and hands the 64-byte
  * handle to the other ranks (any byte transport: torch.distributed broadcast in bench.py); each of them maps the SAME

@@ -168,6 +168,20 @@ double ref_render(void *h, const float *cam, int W, int H, int threads, unsigned
 	return std::chrono::duration<double, std::milli>(t1 - t0).count();
 }
 
+// The farm overload (src/render.h:20-23, src/render.cpp:243-265): tiles coords[4i..] written at data + offsets[i] in
+// the planar delta format of RenderTask::Work with compress == 1.
+double ref_render_tiles(void *h, const float *cam, int resx, int resy, unsigned char *data, const int *coords,
+						const int *offsets, int nTiles, int rank, int threads, unsigned *stats) {
+	RefScene *rs = (RefScene *)h;
+	vector<int> c(coords, coords + (size_t)nTiles * 4), o(offsets, offsets + nTiles);
+	auto t0 = std::chrono::steady_clock::now();
+	TreeStats st = rs->instanced ? Render(rs->dscene, MakeCamera(cam), (uint)resx, (uint)resy, data, c, o, Options(), (uint)rank, (uint)threads)
+								 : Render(rs->scene, MakeCamera(cam), (uint)resx, (uint)resy, data, c, o, Options(), (uint)rank, (uint)threads);
+	auto t1 = std::chrono::steady_clock::now();
+	CopyStats(st, stats);
+	return std::chrono::duration<double, std::milli>(t1 - t0).count();
+}
+
 // Primary packets exactly as RenderTask::Work builds them (src/render.cpp:61-62,112-115) but
 // stopping after geometry.TraversePrimary (src/scene_trace.cpp:119-120): per-pixel nearest hit.
 // Misses: triId = -1, t = +inf.

@@ -50,6 +50,8 @@ def lib(variant: str = "scalar") -> C.CDLL:
     L.ref_set_lights.argtypes = [C.c_void_p, _f32p, C.c_int]
     L.ref_render.restype = C.c_double
     L.ref_render.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, C.c_int, _u8p, _u32p]
+    L.ref_render_tiles.restype = C.c_double
+    L.ref_render_tiles.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, _u8p, _i32p, _i32p, C.c_int, C.c_int, C.c_int, _u32p]
     L.ref_trace_primary.argtypes = [C.c_void_p, _f32p, C.c_int, C.c_int, _i32p, _f32p, _f32p, _u32p]
     L.ref_trace_rays.argtypes = [C.c_void_p, _f32p, _f32p, C.c_void_p, C.c_int, C.c_int, _i32p, _f32p, _f32p]
     L.ref_trace_shadow.argtypes = [C.c_void_p, _f32p, _f32p, _f32p, C.c_int]
@@ -173,6 +175,15 @@ class RefScene:
         stats = np.zeros(4, np.uint32)
         ms = self.L.ref_render(self.h, cam, W, H, threads, img.reshape(-1), stats)
         return img, dict(intersects=int(stats[0]), iters=int(stats[1]), rays=int(stats[2]), skips=int(stats[3])), ms
+
+    def render_tiles(self, cam, W, H, coords, offsets, nbytes, rank=0, threads=1):
+        """Farm overload of Render(): planar delta-coded tiles at data + offsets[i] (src/render.cpp:140-166, 243-265)."""
+        c = np.ascontiguousarray(coords, np.int32).reshape(-1)
+        o = np.ascontiguousarray(offsets, np.int32)
+        data = np.zeros(nbytes, np.uint8)
+        stats = np.zeros(4, np.uint32)
+        self.L.ref_render_tiles(self.h, cam, W, H, data, c, o, len(o), rank, threads, stats)
+        return data, dict(intersects=int(stats[0]), iters=int(stats[1]), rays=int(stats[2]), skips=int(stats[3]))
 
     def trace_primary(self, cam, W, H):
         tri = np.zeros((H, W), np.int32)

@@ -19,7 +19,7 @@ ABI_SYMBOLS = [
     "snl_last_error", "snl_abi_version", "snl_device_count", "snl_scene_create", "snl_scene_destroy",
     "snl_scene_set_geometry", "snl_scene_set_materials", "snl_scene_set_lights", "snl_set_options",
     "snl_scene_load_obj", "snl_scene_counts", "snl_scene_copy_host_bvh", "snl_scene_bbox", "snl_trace_primary",
-    "snl_trace_rays", "snl_trace_shadow", "snl_raytrace", "snl_render", "snl_render_dev", "snl_scene_sync",
+    "snl_trace_rays", "snl_trace_shadow", "snl_raytrace", "snl_render", "snl_render_dev", "snl_render_farm", "snl_scene_sync",
     "snl_scene_launch_count", "snl_scene_stream", "snl_host_scene_load_obj", "snl_host_scene_free",
     "snl_host_scene_counts", "snl_host_scene_copy", "snl_host_scene_material", "snl_host_scene_texture",
     "snl_scene_set_host_scene", "snl_scene_build_device", "snl_scene_build_ms", "snl_scene_set_instances",
@@ -133,6 +133,7 @@ def load_library(counters: bool = False) -> C.CDLL:
     L.snl_raytrace.argtypes = [vp, fp, fp, vp, i, i, fp, C.POINTER(Stats)]
     L.snl_render.argtypes = [vp, C.POINTER(Camera), i, i, vp, i, vp, C.c_size_t, i, C.POINTER(Stats)]
     L.snl_render_dev.argtypes = [vp, C.POINTER(Camera), i, i, vp, i, vp, C.c_size_t, i]
+    L.snl_render_farm.argtypes = [vp, C.POINTER(Camera), i, i, vp, vp, vp, i, i, C.POINTER(Stats)]
     L.snl_scene_sync.argtypes = [vp, C.POINTER(Stats)]
     L.snl_scene_launch_count.restype = C.c_uint64
     L.snl_scene_launch_count.argtypes = [vp]
@@ -407,6 +408,22 @@ class Scene:
         self._check(self.L.snl_render(self.h, C.byref(cam), W, H, _ptr(t), 0 if t is None else len(t), _ptr(out),
                                       out.strides[0], rank, C.byref(st)))
         return out, st.as_dict()
+
+    def render_farm(self, cam: Camera, W, H, coords, offsets=None, data=None, rank=0):
+        """The farm overload of Render() (src/render.h:20-23): tiles `coords` (x, y, w, h) written at data + offsets[i]
+        as planar x, y - x, z - x byte planes (src/render.cpp:140-166). offsets default to back-to-back tiles.
+        Returns (data, offsets, stats)."""
+        c = np.ascontiguousarray(coords, np.int32).reshape(-1, 4)
+        sizes = c[:, 2].astype(np.int64) * c[:, 3] * 3
+        if offsets is None:
+            offsets = np.concatenate([[0], np.cumsum(sizes)[:-1]]) if len(c) else np.zeros(0)
+        o = np.ascontiguousarray(offsets, np.int32)
+        if data is None:
+            data = np.zeros(int((o + sizes).max()) if len(c) else 1, np.uint8)
+        st = Stats()
+        self._check(self.L.snl_render_farm(self.h, C.byref(cam), W, H, _ptr(data), _ptr(c), _ptr(o), len(c), rank,
+                                           C.byref(st)))
+        return data, o, st.as_dict()
 
     def render_dev(self, cam: Camera, W, H, dev_ptr: int, pitch: int, tiles=None, rank=0):
         """Render() into device memory (e.g. a torch uint8 tensor's data_ptr()); asynchronous until sync()."""

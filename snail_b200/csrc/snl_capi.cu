@@ -1054,6 +1054,44 @@ int snl_render(snl_scene *s, const snl_camera *cam, int W, int H, const int *til
 	return sync_and_stats(s, stats);
 }
 
+int snl_render_farm(snl_scene *s, const snl_camera *cam, int W, int H, unsigned char *data, const int *coords,
+					const int *offsets, int nTiles, int rank, snl_stats *stats) {
+	SNL_REQUIRE(s && cam && data && coords && offsets && W > 0 && H > 0 && nTiles >= 0, SNL_ERR_INVALID, "bad argument");
+	size_t lo = ~(size_t)0, hi = 0, sum = 0;
+	for(int i = 0; i < nTiles; i++) {
+		const int w = coords[i * 4 + 2], h = coords[i * 4 + 3];
+		SNL_REQUIRE(offsets[i] >= 0 && w > 0 && h > 0, SNL_ERR_INVALID, "bad tile / offset");
+		const size_t bytes = (size_t)w * h * 3;
+		lo = std::min(lo, (size_t)offsets[i]);
+		hi = std::max(hi, (size_t)offsets[i] + bytes);
+		sum += bytes;
+	}
+	SNL_REQUIRE(hi < ((size_t)1 << 31), SNL_ERR_INVALID, "tile buffer too large");
+	SNL_TRY(begin_call(s));
+	const size_t dpitch = (size_t)W * 3;
+	SNL_CUDA(s->dImage.reserve(dpitch * H));
+	SNL_TRY(render_common(s, cam, W, H, coords, nTiles, s->dImage.ptr, dpitch, rank));  // validates the rectangles
+	if(nTiles > 0) {
+		SNL_CUDA(s->dFarmTiles.reserve(nTiles));
+		SNL_CUDA(s->dFarmOffsets.reserve(nTiles));
+		SNL_CUDA(s->dFarm.reserve(hi));
+		SNL_CUDA(cudaMemcpyAsync(s->dFarmTiles.ptr, coords, (size_t)nTiles * sizeof(int4), cudaMemcpyHostToDevice, s->stream));
+		SNL_CUDA(cudaMemcpyAsync(s->dFarmOffsets.ptr, offsets, (size_t)nTiles * sizeof(int), cudaMemcpyHostToDevice, s->stream));
+		SNL_CUDA(launch_farm_pack(s->dImage.ptr, dpitch, s->dFarmTiles.ptr, s->dFarmOffsets.ptr, nTiles, s->dFarm.ptr, s->stream));
+		s->launches++;
+	}
+	SNL_TRY(end_call(s));
+	if(nTiles > 0) {
+		if(sum == hi - lo)  // the tiles fill [lo, hi) (server.cpp lays them out back to back): one copy
+			SNL_CUDA(cudaMemcpyAsync(data + lo, s->dFarm.ptr + lo, hi - lo, cudaMemcpyDeviceToHost, s->stream));
+		else
+			for(int i = 0; i < nTiles; i++)
+				SNL_CUDA(cudaMemcpyAsync(data + offsets[i], s->dFarm.ptr + offsets[i],
+										 (size_t)coords[i * 4 + 2] * coords[i * 4 + 3] * 3, cudaMemcpyDeviceToHost, s->stream));
+	}
+	return sync_and_stats(s, stats);
+}
+
 // ---- frames shared between the ranks of one box (CUDA IPC over NVLink) ----------------------------------------------
 
 int snl_frame_create(snl_scene *s, int W, int H, void **bgr8_dev, unsigned char ipc_handle[SNL_IPC_HANDLE_BYTES]) {

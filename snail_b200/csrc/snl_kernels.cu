@@ -345,4 +345,50 @@ cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenPara
 	return cudaGetLastError();
 }
 
+// Farm tile format of Render(scene, camera, resx, resy, data, coords, offsets, ...) (src/render.cpp:140-166, compress == 1):
+// every tile is three w*h byte planes, colour.x, colour.y - colour.x, colour.z - colour.x (mod 256). The frame holds
+// ConvColor's byte order (z, y, x per pixel, src/render.cpp:11-17), so this is a pure byte shuffle of bytes that are
+// already the reference's. One CTA per tile; 4 pixels (12 frame bytes, three 32-bit words) per thread when aligned.
+__global__ void __launch_bounds__(256) k_farm_pack(const unsigned char *__restrict__ frame, size_t pitch, const int4 *__restrict__ tiles,
+													const int *__restrict__ offsets, unsigned char *__restrict__ out) {
+	const int4 t = tiles[blockIdx.x];
+	const int x = t.x, y = t.y, w = t.z, h = t.w;
+	unsigned char *dst = out + offsets[blockIdx.x];
+	const size_t plane = (size_t)w * h;
+	const bool fast = !(w & 3) && !(x & 3) && !(pitch & 3) && !(offsets[blockIdx.x] & 3) && !((size_t)frame & 3) && !((size_t)out & 3);
+	if(fast) {
+		const int wq = w >> 2;
+		for(int i = threadIdx.x; i < wq * h; i += blockDim.x) {
+			const int ty = i / wq, tx = (i - ty * wq) * 4;
+			const uint32_t *p = (const uint32_t *)(frame + (size_t)(y + ty) * pitch + (size_t)(x + tx) * 3);
+			const uint32_t a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+			// bytes: z0 y0 x0 z1 | y1 x1 z2 y2 | x2 z3 y3 x3
+			const uint32_t X = ((a >> 16) & 255u) | (b & 0xff00u) | ((c & 255u) << 16) | (c & 0xff000000u);
+			const uint32_t Y = ((a >> 8) & 255u) | ((b & 255u) << 8) | ((b >> 24) << 16) | (((c >> 16) & 255u) << 24);
+			const uint32_t Z = (a & 255u) | ((a >> 24) << 8) | (((b >> 16) & 255u) << 16) | (((c >> 8) & 255u) << 24);
+			const uint32_t o = ty * w + tx;
+			*(uint32_t *)(dst + o) = X;
+			*(uint32_t *)(dst + plane + o) = __vsub4(Y, X);
+			*(uint32_t *)(dst + 2 * plane + o) = __vsub4(Z, X);
+		}
+	}
+	else
+		for(int i = threadIdx.x; i < w * h; i += blockDim.x) {
+			const int ty = i / w, tx = i - ty * w;
+			const unsigned char *p = frame + (size_t)(y + ty) * pitch + (size_t)(x + tx) * 3;
+			const unsigned char X = p[2];
+			dst[i] = X;
+			dst[plane + i] = (unsigned char)(p[1] - X);
+			dst[2 * plane + i] = (unsigned char)(p[0] - X);
+		}
+}
+
+cudaError_t launch_farm_pack(const unsigned char *frame, size_t pitch, const int4 *tiles, const int *offsets, int nTiles,
+							 unsigned char *out, cudaStream_t st) {
+	if(nTiles <= 0)
+		return cudaSuccess;
+	k_farm_pack<<<nTiles, 256, 0, st>>>(frame, pitch, tiles, offsets, out);
+	return cudaGetLastError();
+}
+
 }  // namespace snl

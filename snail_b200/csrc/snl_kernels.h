@@ -25,6 +25,10 @@ cudaError_t launch_raytrace(const SceneDev &S, const PreSet &pre, const float *o
 cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, const int4 *packets,
 						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st);
 
+// Farm tile format (src/render.cpp:140-166): frame tiles -> planar x, y - x, z - x byte planes at out + offsets[i].
+cudaError_t launch_farm_pack(const unsigned char *frame, size_t pitch, const int4 *tiles, const int *offsets, int nTiles,
+							 unsigned char *out, cudaStream_t st);
+
 // Wavefront form of launch_render for frames with the reflection bounce (snl_wavefront.cu). *launches = kernels issued.
 cudaError_t launch_render_wavefront(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H,
 									const int4 *packets, int nPackets, const WfBuffers &B, int persistentCtas,

@@ -105,6 +105,9 @@ struct snl_scene {
 	std::vector<int> lastTiles;
 	snl::DevBuf<int4> dPackets;
 	int nPackets = 0;
+	snl::DevBuf<int4> dFarmTiles;  // snl_render_farm: tile rectangles, their offsets, the packed tiles
+	snl::DevBuf<int> dFarmOffsets;
+	snl::DevBuf<unsigned char> dFarm;
 
 	uint64_t launches = 0;
 

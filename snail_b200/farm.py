@@ -171,3 +171,16 @@ class Farm:
             self.dist.barrier()
             if self.rank == 0:
                 self.scene.frame_close(self.frame)
+
+
+def decode_farm_tiles(data: np.ndarray, coords, offsets, W: int, H: int, out: np.ndarray | None = None) -> np.ndarray:
+    """What the client does with the farm wire format (DecompressTask, src/compression.cpp:112-142): planes
+    x, y - x, z - x of every tile back into an (H, W, 3) frame in ConvColor byte order (byte 2 = x)."""
+    img = np.zeros((H, W, 3), np.uint8) if out is None else out
+    c = np.asarray(coords, np.int64).reshape(-1, 4)
+    for (x, y, w, h), off in zip(c, np.asarray(offsets, np.int64)):
+        p = np.asarray(data[off:off + 3 * w * h], np.uint8).reshape(3, h, w)
+        img[y:y + h, x:x + w, 2] = p[0]
+        img[y:y + h, x:x + w, 1] = p[1] + p[0]
+        img[y:y + h, x:x + w, 0] = p[2] + p[0]
+    return img

@@ -130,6 +130,66 @@ def instanced_cases(manifest):
         ref.close()
 
 
+FARM_CASES = {"box": 1, "barracks_tex": 1, "panes": 1}  # CASES entries also rendered through the farm overload
+FARM_W, FARM_H = 128, 128  # 8 x 2 tiles of blockWidth x blockHeight = 16 x 64 (src/rtbase_math.h:31-34)
+
+
+def farm_cases(manifest):
+    """Render(scene, camera, resx, resy, data, coords, offsets, options, rank, threads) (src/render.cpp:243-265): the
+    planar delta-coded 16x64 tiles the farm nodes produce. Two tile sets per scene: (A) every tile, back to back in a
+    shuffled order, gVals[8] rank tint with rank 5; (B) every other tile with gaps between them, no tint."""
+    from snail_b200 import farm
+    W, H = FARM_W, FARM_H
+    for name in FARM_CASES:
+        obj, mtl, inside, _, _ = CASES[name]
+        mtl_path = os.path.join(DATA, mtl) if mtl else None
+        obj_path = os.path.join(DATA, obj[1:]) if obj.startswith("@") else os.path.join(SCENES, obj)
+        ref = R.RefScene(obj_path, mtl_path, TEXDIR if mtl else "", variant="scalar")
+        bmin, bmax = ref.bbox()
+        cam, light = R.bench_camera(bmin, bmax, inside=inside)
+        if name in VIEWS:
+            cam = R.camera_array(VIEWS[name][0])
+            light = np.array(VIEWS[name][1], np.float32)
+        hs = sb.HostScene(obj_path, mtl_path, TEXDIR if mtl else "")
+        hn, ht, hsh, hm = hs.bvh()
+        orc = O.OracleScene(hn, ht, hsh, hm, hs.materials(), hs.textures())
+        tiles = farm.divide_image(W, H)
+        rng = np.random.default_rng(11)
+        out = {"camera": cam, "light": light, "size": np.array([W, H], np.int32)}
+        ref.set_lights([light])
+        orc.set_lights([light])
+        tri, _, _ = ref.trace_primary(cam, W, H)
+        lane0 = np.repeat(tri[:, 0::4], 4, axis=1)[:, :W]
+        for tag, gv, rank, sel, stride in (("A", {6: 1, 7: 1, 8: 1}, 5, rng.permutation(len(tiles)), 3072),
+                                           ("B", {6: 1, 7: 1}, 0, np.arange(0, len(tiles), 2), 4096)):
+            coords = tiles[sel]
+            offsets = (np.arange(len(coords)) * stride).astype(np.int32)
+            ref.set_gvals(gv)
+            data, st = ref.render_tiles(cam, W, H, coords, offsets, int(offsets.max()) + 3072, rank=rank)
+            # the same tiles through the image overload must hold the same bytes (sanity of the generator itself)
+            img, _, _ = ref.render(cam, W, H, threads=1)
+            dec = farm.decode_farm_tiles(data, coords, offsets, W, H)
+            orc.set_gvals({k: v for k, v in gv.items() if k != 8})
+            u = np.zeros((H, W), np.uint8)
+            orc.render(cam, W, H, undef=u)
+            undef = (u != 0) | ((tri == 0) & (lane0 < 0))
+            for x, y, w, h in (coords if not gv.get(8) else []):  # the image overload tints with rank 0
+                ok = (dec[y:y + h, x:x + w] == img[y:y + h, x:x + w]).all(axis=2) | undef[y:y + h, x:x + w]
+                assert ok.all(), (name, tag, x, y)
+            out["coords_" + tag], out["offsets_" + tag], out["data_" + tag] = coords, offsets, data
+            out["rank_" + tag] = np.int32(rank)
+            out["gvals_" + tag] = np.array([[k, v] for k, v in gv.items()], np.int32)
+            out["undef_" + tag] = undef
+            out["rays_" + tag] = np.int64(st["rays"])
+        np.savez_compressed(os.path.join(GOLDEN, "farm_" + name + ".npz"), **out)
+        manifest["farm"][name] = {"W": W, "H": H, "tiles_A": int(len(out["coords_A"])), "tiles_B": int(len(out["coords_B"])),
+                                  "rays_A": int(out["rays_A"]), "rays_B": int(out["rays_B"]),
+                                  "undef_A": int(out["undef_A"].sum()), "sha256_data_A": sha(out["data_A"])}
+        print("farm", name, manifest["farm"][name])
+        orc.close()
+        ref.close()
+
+
 def sha(a: np.ndarray) -> str:
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
 
@@ -216,6 +276,8 @@ def main():
         ref.close()
     manifest["instanced"] = {}
     instanced_cases(manifest)
+    manifest["farm"] = {}
+    farm_cases(manifest)
     with open(os.path.join(GOLDEN, "manifest.json"), "w") as f:
         json.dump(manifest, f, indent=1, sort_keys=True)
 
