@@ -351,6 +351,14 @@ void snl_scene_destroy(snl_scene *s) {
 		cudaEventDestroy(s->ev0);
 	if(s->ev1)
 		cudaEventDestroy(s->ev1);
+	if(s->forkEv)
+		cudaEventDestroy(s->forkEv);
+	for(int b = 0; b < snl_scene::kBands; b++) {
+		if(s->bandEv[b])
+			cudaEventDestroy(s->bandEv[b]);
+		if(s->bandStream[b])
+			cudaStreamDestroy(s->bandStream[b]);
+	}
 	if(s->stream)
 		cudaStreamDestroy(s->stream);
 	delete s;
@@ -916,8 +924,10 @@ static const float kRankTint[16][3] = {  // src/render.cpp:119-128
 	{1.0f, 1.0f, 0.6f}, {1.0f, 1.0f, 1.0f}, {0.3f, 0.3f, 0.3f}, {0.3f, 0.3f, 1.0f}, {0.3f, 0.7f, 0.3f}, {0.3f, 0.7f, 0.7f},
 	{0.7f, 0.3f, 0.3f}, {0.7f, 0.3f, 0.7f}, {0.7f, 0.7f, 0.3f}, {0.7f, 1.7f, 0.7f}};
 
+// hostOut != null (snl_render): a large full frame is rendered in row bands, each on its own stream and followed by the
+// device->host copy of its rows; *hostDone tells the caller the copies are already queued (and joined into s->stream).
 static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, const int *tiles, int nTiles, unsigned char *dOut,
-						 size_t pitch, int rank) {
+						 size_t pitch, int rank, unsigned char *hostOut = nullptr, size_t hostPitch = 0, bool *hostDone = nullptr) {
 	SceneDev S;
 	SNL_TRY(make_scene_dev(s, S));
 	SNL_REQUIRE(!(S.instances && S.gvSuper), SNL_ERR_UNSUPPORTED, "gVals[9] supersampling is not available on an instanced scene");
@@ -1013,6 +1023,34 @@ static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, cons
 		SNL_CUDA(cudaEventRecord(s->ev0, s->stream));
 	}
 	const int variant = T.choice;
+	const char *bandsEnv = getenv("SNL_RENDER_BANDS");  // "0": one launch, copy afterwards
+	if(hostOut && hostDone && !packets && nPk >= 8 * s->smCount && !(bandsEnv && bandsEnv[0] == '0')) {
+		if(!s->forkEv) {
+			SNL_CUDA(cudaEventCreateWithFlags(&s->forkEv, cudaEventDisableTiming));
+			for(int b = 0; b < snl_scene::kBands; b++) {
+				SNL_CUDA(cudaStreamCreateWithFlags(&s->bandStream[b], cudaStreamNonBlocking));
+				SNL_CUDA(cudaEventCreateWithFlags(&s->bandEv[b], cudaEventDisableTiming));
+			}
+		}
+		const int px = (W + 15) / 16, py = (H + 15) / 16;
+		SNL_CUDA(cudaEventRecord(s->forkEv, s->stream));
+		for(int b = 0; b < snl_scene::kBands; b++) {
+			const int r0 = py * b / snl_scene::kBands, r1 = py * (b + 1) / snl_scene::kBands;
+			if(r1 <= r0)
+				continue;
+			cudaStream_t st = s->bandStream[b];
+			SNL_CUDA(cudaStreamWaitEvent(st, s->forkEv, 0));
+			SNL_CUDA(launch_render(S, s->originPre.set(), g, W, H, nullptr, 0, dOut, pitch, variant, st, r0 * px, (r1 - r0) * px));
+			s->launches++;
+			const int y0 = r0 * 16, y1 = std::min(H, r1 * 16);
+			SNL_CUDA(cudaMemcpy2DAsync(hostOut + (size_t)y0 * hostPitch, hostPitch, dOut + (size_t)y0 * pitch, pitch, (size_t)W * 3,
+									   y1 - y0, cudaMemcpyDeviceToHost, st));
+			SNL_CUDA(cudaEventRecord(s->bandEv[b], st));
+			SNL_CUDA(cudaStreamWaitEvent(s->stream, s->bandEv[b], 0));
+		}
+		*hostDone = true;
+		return SNL_OK;
+	}
 	SNL_CUDA(launch_render(S, s->originPre.set(), g, W, H, packets, s->nPackets, dOut, pitch, variant, s->stream));
 	s->launches++;
 	return SNL_OK;
@@ -1040,9 +1078,12 @@ int snl_render(snl_scene *s, const snl_camera *cam, int W, int H, const int *til
 	SNL_TRY(begin_call(s));
 	const size_t dpitch = (size_t)W * 3;
 	SNL_CUDA(s->dImage.reserve(dpitch * H));
-	SNL_TRY(render_common(s, cam, W, H, tiles_xywh, nTiles, s->dImage.ptr, dpitch, rank));
+	bool copied = false;
+	SNL_TRY(render_common(s, cam, W, H, tiles_xywh, nTiles, s->dImage.ptr, dpitch, rank, bgr8_host, pitch, &copied));
 	SNL_TRY(end_call(s));
-	if(!tiles_xywh)
+	if(copied)
+		;  // row bands: every band's copy is already queued behind its kernel
+	else if(!tiles_xywh)
 		SNL_CUDA(cudaMemcpy2DAsync(bgr8_host, pitch, s->dImage.ptr, dpitch, dpitch, H, cudaMemcpyDeviceToHost, s->stream));
 	else
 		for(int i = 0; i < nTiles; i++) {

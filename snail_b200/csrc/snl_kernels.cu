@@ -193,18 +193,19 @@ __device__ __forceinline__ unsigned conv_channel(float c) {
 template <int FLAGS, bool SUPER, int MINB>
 __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreSet pre, RayGenParams g, int W, int H,
 												 int packetsX, const int4 *__restrict__ packets,
-												 unsigned char *__restrict__ out, size_t pitch) {
+												 unsigned char *__restrict__ out, size_t pitch, int firstPacket) {
 	int px0, py0, cw, ch;
+	const int packet = blockIdx.x + firstPacket;
 	if(packets) {
-		const int4 p = packets[blockIdx.x];
+		const int4 p = packets[packet];
 		px0 = p.x;
 		py0 = p.y;
 		cw = p.z;
 		ch = p.w;
 	}
 	else {
-		px0 = (blockIdx.x % packetsX) * 16;
-		py0 = (blockIdx.x / packetsX) * 16;
+		px0 = (packet % packetsX) * 16;
+		py0 = (packet / packetsX) * 16;
 		cw = min(16, W - px0);
 		ch = min(16, H - py0);
 	}
@@ -322,26 +323,27 @@ cudaError_t launch_raytrace(const SceneDev &S, const PreSet &pre, const float *o
 }
 
 cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, const int4 *packets,
-						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st) {
+						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st, int first, int count) {
 	const int px = (W + 15) / 16, py = (H + 15) / 16;
-	const int grid = packets ? nPackets : px * py;
-	if(grid <= 0)
+	const int all = packets ? nPackets : px * py;
+	const int grid = count < 0 ? all - first : count;
+	if(grid <= 0 || first < 0 || first + grid > all)
 		return cudaSuccess;
 	const int MB = SNL_RENDER_MIN_BLOCKS;
 	if(S.instances)  // Scene<DBVH>: simple shading only, so no transparency; supersampling is refused by the caller
-		k_render<2, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+		k_render<2, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first);
 	else if(S.hasTransp) {
 		if(S.gvSuper)
-			k_render<1, true, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+			k_render<1, true, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first);
 		else
-			k_render<1, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+			k_render<1, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first);
 	}
 	else if(S.gvSuper)
-		k_render<0, true, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+		k_render<0, true, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first);
 	else if(variant == 1)
-		k_render<0, false, MB + 1><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+		k_render<0, false, MB + 1><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first);
 	else
-		k_render<0, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch);
+		k_render<0, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first);
 	return cudaGetLastError();
 }
 

@@ -22,8 +22,11 @@ cudaError_t launch_trace_shadow(const SceneDev &S, const PreSet &pre, const floa
 								int n, cudaStream_t st);
 cudaError_t launch_raytrace(const SceneDev &S, const PreSet &pre, const float *o3, const float *d3,
 							const unsigned char *mask, int n, bool shared, float *rgb3, cudaStream_t st);
+// packets == null: the full image, packet p = (p % packetsX, p / packetsX); first / count then pick a sub-range of the
+// packets (count < 0: all of them).
 cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, const int4 *packets,
-						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st);
+						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st, int first = 0,
+						  int count = -1);
 
 // Farm tile format (src/render.cpp:140-166): frame tiles -> planar x, y - x, z - x byte planes at out + offsets[i].
 cudaError_t launch_farm_pack(const unsigned char *frame, size_t pitch, const int4 *tiles, const int *offsets, int nTiles,

@@ -57,6 +57,11 @@ struct snl_scene {
 	int device = 0;
 	cudaStream_t stream = nullptr;
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	// snl_render to a host image: the frame is rendered as kBands row bands on their own streams, each followed by the
+	// device->host copy of its rows, so all but the last band's copy overlaps the rendering of the bands after it
+	enum { kBands = 4 };
+	cudaStream_t bandStream[kBands] = {nullptr, nullptr, nullptr, nullptr};
+	cudaEvent_t bandEv[kBands] = {nullptr, nullptr, nullptr, nullptr}, forkEv = nullptr;
 	bool evPending = false;
 
 	// k_render comes in two register budgets (snl_kernels.cu, MINB); the first frame of a workload is rendered with

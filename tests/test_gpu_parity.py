@@ -342,3 +342,26 @@ def test_wavefront_pipeline_equals_fused_kernel(sb, name, inside, W, H, monkeypa
     assert (a[0] == b[0]).all() and (a[2] == b[2]).all()
     for k in ("rays", "primary", "shadow", "reflection", "reflection_shadow"):
         assert a[1][k] == b[1][k] and a[3][k] == b[3][k], k
+
+
+def test_banded_host_render_equals_single_launch(sb):
+    """snl_render to a host image renders large full frames as row bands with the device->host copies overlapped
+    (snl_capi.cu render_common); the frame and the ray counts must be those of the single launch."""
+    import os
+    sc = sb.Scene(0)
+    sc.load_obj(scene_path("lancia"))
+    cam, light = sb.bench_camera(*sc.bbox())
+    sc.set_options({7: 1})
+    sc.set_lights([light])
+    W, H = 1920, 1080 - 8  # ragged last packet row
+    out = {}
+    for bands in ("0", "1"):
+        os.environ["SNL_RENDER_BANDS"] = bands
+        img = np.full((H, W + 5, 3), 7, np.uint8)[:, :W]  # pitch > 3 * W
+        sc.render(cam, W, H, out=img)
+        _, st = sc.render(cam, W, H, out=img)
+        out[bands] = (img.copy(), st["rays"])
+    os.environ.pop("SNL_RENDER_BANDS")
+    assert (out["0"][0] == out["1"][0]).all() and out["0"][1] == out["1"][1]
+    assert out["1"][0].any()
+    sc.close()
