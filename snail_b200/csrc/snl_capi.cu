@@ -197,7 +197,11 @@ int ensure_pre(snl_scene *s, PreCacheEntry &e, const float origin[3]) {
 	return SNL_OK;
 }
 
-int make_scene_dev(snl_scene *s, SceneDev &S) {
+// shareOrigin (the camera position of a Render() call): a light sitting exactly there - the reference's own way of
+// placing a light, src/rtracer.cpp:270-281 - shares the camera's per-origin triangle records instead of getting a
+// second identical copy (half the PreTri bytes competing for L1 / L2, one k_pretransform less per frame). The caller
+// fills S.lightPre[i] for the lights flagged in *shared once the camera's records are up to date.
+int make_scene_dev(snl_scene *s, SceneDev &S, const float *shareOrigin = nullptr, unsigned *shared = nullptr) {
 	memset(&S, 0, sizeof(S));
 	S.nodes = s->dNodes.ptr;
 	S.gtris = s->dTris.ptr;
@@ -212,10 +216,15 @@ int make_scene_dev(snl_scene *s, SceneDev &S) {
 	S.nLights = (int)s->lights.size();
 	for(int i = 0; i < S.nLights; i++) {
 		const snl_light &l = s->lights[i];
-		int r = ensure_pre(s, s->lightPre[i], l.pos);
-		if(r)
-			return r;
-		S.lightPre[i] = s->lightPre[i].set();
+		const char *shareEnv = getenv("SNL_SHARE_PRE");  // "0": every light gets its own records (A/B)
+		if(shareOrigin && shared && memcmp(l.pos, shareOrigin, 12) == 0 && !(shareEnv && shareEnv[0] == '0'))
+			*shared |= 1u << i;
+		else {
+			int r = ensure_pre(s, s->lightPre[i], l.pos);
+			if(r)
+				return r;
+			S.lightPre[i] = s->lightPre[i].set();
+		}
 		memcpy(S.lights[i].pos, l.pos, 12);
 		memcpy(S.lights[i].color, l.color, 12);
 		S.lights[i].radius = l.radius;
@@ -929,13 +938,17 @@ static const float kRankTint[16][3] = {  // src/render.cpp:119-128
 static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, const int *tiles, int nTiles, unsigned char *dOut,
 						 size_t pitch, int rank, unsigned char *hostOut = nullptr, size_t hostPitch = 0, bool *hostDone = nullptr) {
 	SceneDev S;
-	SNL_TRY(make_scene_dev(s, S));
+	unsigned sharedLights = 0;
+	SNL_TRY(make_scene_dev(s, S, cam->pos, &sharedLights));
 	SNL_REQUIRE(!(S.instances && S.gvSuper), SNL_ERR_UNSUPPORTED, "gVals[9] supersampling is not available on an instanced scene");
 	if(s->gVals[8]) {
 		S.gvTint = 1;
 		memcpy(S.tint, kRankTint[(unsigned)rank % 16], 12);
 	}
 	SNL_TRY(ensure_pre(s, s->originPre, cam->pos));
+	for(int i = 0; i < S.nLights; i++)
+		if(sharedLights >> i & 1)
+			S.lightPre[i] = s->originPre.set();
 	RayGenParams g;
 	const int scale = s->gVals[9] ? 2 : 1;  // src/render.cpp:60-62
 	make_raygen(*cam, W * scale, H * scale, g);
