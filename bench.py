@@ -179,9 +179,9 @@ def load_traffic(name, W, H):
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
         e = t.get(f"{name}@{W}x{H}")
-        return (int(e["dram_bytes_per_launch"]), e["source"]) if e else (None, None)
+        return (int(e["dram_bytes_per_launch"]), e["source"], e.get("ncu")) if e else (None, None, None)
     except Exception:
-        return None, None
+        return None, None, None
 
 
 def run_ours(args, w, W, H):
@@ -362,7 +362,7 @@ def run_ours(args, w, W, H):
         abytes, cst = algorithmic_bytes(sb, w, W, H, cam, light)
         if abytes:
             ach = abytes / (total_ms / K * 1e-3) / 1e9
-            traffic, tsrc = load_traffic(w["name"], W, H)
+            traffic, tsrc, ncu_sm = load_traffic(w["name"], W, H)
             line["roofline"] = {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
                                 "frac": round(ach / peak, 4), "traffic": traffic, "traffic_source": tsrc,
                                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
@@ -372,6 +372,8 @@ def run_ours(args, w, W, H):
                                         "(see DESIGN.md, profiles/)",
                                 "algorithmic_bytes_per_launch": int(abytes),
                                 "node_visits": cst["node_visits"], "tri_tests": cst["tri_tests"] + cst["gtri_tests"]}
+            if ncu_sm:  # what actually binds the kernel, from the committed ncu capture (not measured in this run)
+                line["roofline"]["sm_limiters_from_ncu"] = ncu_sm
     if world == 1 and not args.no_cpu_baseline:
         threads = host_threads()
         reference_frames(w, W, H, 1, threads)

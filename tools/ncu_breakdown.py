@@ -84,6 +84,23 @@ def main():
     print(f"\nwarp instructions: {tot}")
     for k, (w, t) in sorted(agg.items(), key=lambda kv: -kv[1][0]):
         print(f"  {k:24s} {w / tot * 100:5.1f}% of warp-inst   avg active lanes {t / max(w, 1):5.1f}")
+    # dynamic opcode mix by issue pipe (B300_MICROARCH.md: FFMA/FMUL/FADD/IMAD on the fma pipe, FMNMX/IADD3/LOP3/SEL/ISETP/
+    # FSETP/MOV... on the alu pipe, each one warp instruction per 2 cycles per SMSP)
+    fma = {"FFMA", "FMUL", "FADD", "IMAD", "HFMA2", "FFMA2", "FMUL2", "FADD2"}
+    alu = {"FMNMX", "FMNMX3", "IADD3", "LOP3", "SHF", "PRMT", "ISETP", "FSETP", "SEL", "FSEL", "MOV", "PLOP3", "IABS", "LEA",
+           "VIADD", "VIMNMX", "IMNMX", "I2FP", "VOTE", "FCHK", "IADD", "VIMNMX3", "UISETP", "VIADDMNMX"}
+    ops, pipes = {}, {}
+    for (_, sass, w, _t) in seen.values():
+        m = re.match(r"(@!?U?P\d+\s+)?([A-Z0-9_]+)", sass)
+        if not m:
+            continue
+        op = m.group(2)
+        ops[op] = ops.get(op, 0) + w
+        pipe = "fma" if op in fma else "alu" if op in alu else "lsu" if re.match(r"LD|ST|ATOM|RED", op) else \
+            "control" if op in ("BRA", "BSSY", "BSYNC", "WARPSYNC", "CALL", "RET", "EXIT", "BAR", "BREAK", "NOP") else "other"
+        pipes[pipe] = pipes.get(pipe, 0) + w
+    print("\nissue pipes: " + "  ".join(f"{k} {v / tot * 100:.1f}%" for k, v in sorted(pipes.items(), key=lambda kv: -kv[1])))
+    print("opcodes:     " + "  ".join(f"{k} {v / tot * 100:.1f}%" for k, v in sorted(ops.items(), key=lambda kv: -kv[1])[:16]))
     if "--sass" in sys.argv:
         pat = sys.argv[sys.argv.index("--sass") + 1]
         for addr, ((f, line), sass, w, t) in sorted(seen.items(), key=lambda kv: int(kv[0], 16)):
