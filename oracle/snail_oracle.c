@@ -556,11 +556,38 @@ static void packet_raytrace_ex(oracle_scene *s, const OPacket *pk, int level, in
 						sm[i].diff[c] = tcol[i][c] + (sm[i].diff[c] - tcol[i][c]) * sm[i].opacity;
 		}
 	}
+	/* per-packet light cull (src/scene_trace.cpp:139-140,164-165,494-499): the box of the packet's hit points against each
+	   light's radius, BoxPointDistanceSq of src/funcs.cpp:8-50 */
+	unsigned char lightOn[64];
+	{
+		float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+		for(int i = 0; i < pk->n; i++)
+			if(sel[i])
+				for(int c = 0; c < 3; c++) {
+					lo[c] = sm[i].p[c] < lo[c] ? sm[i].p[c] : lo[c];
+					hi[c] = sm[i].p[c] > hi[c] ? sm[i].p[c] : hi[c];
+				}
+		for(int li = 0; li < s->nLights && li < 64; li++) {
+			const float *p = s->lights[li].pos;
+			float sq = 0.0f;
+			for(int c = 0; c < 3; c++) {
+				if(p[c] < lo[c]) {
+					const float d = p[c] - lo[c];
+					sq += d * d;
+				}
+				else if(p[c] > hi[c]) {
+					const float d = p[c] - hi[c];
+					sq += d * d;
+				}
+			}
+			lightOn[li] = !(sq > s->lights[li].radSq);
+		}
+	}
 	for(int i = 0; i < pk->n; i++) {
 		if(s->nLights) {
 			float ld[3] = {s->ambient[0], s->ambient[1], s->ambient[2]}, ls[3] = {0.0f, 0.0f, 0.0f};
 			for(int li = 0; li < s->nLights; li++)
-				if(sel[i] && trace_light(s, &s->lights[li], &sm[i], ld, ls))
+				if(lightOn[li & 63] && sel[i] && trace_light(s, &s->lights[li], &sm[i], ld, ls))
 					s->rays[level ? 3 : 1]++;
 			for(int c = 0; c < 3; c++)
 				out[i][c] = sm[i].diff[c] * ld[c] + sm[i].spec[c] * ls[c];

@@ -225,6 +225,33 @@ int make_scene_dev(snl_scene *s, SceneDev &S, const float *shareOrigin = nullptr
 				return r;
 			S.lightPre[i] = s->lightPre[i].set();
 		}
+		{
+			// can BoxPointDistanceSq(box of a packet's hit points, light) ever exceed radSq? Hit points lie in the scene box
+			// (instanced: the top-level box), so a light whose farthest box corner is within its radius is never culled and
+			// the kernels skip the packet-wide reduction for it. 1 % margin for the rounding of dir * t + origin.
+			const float *bmin, *bmax;
+			if(!s->instances.empty() && !s->topNodes.empty()) {
+				bmin = s->topNodes[0].bmin;
+				bmax = s->topNodes[0].bmax;
+			}
+			else if(s->devBuilt) {
+				bmin = s->devBBox;
+				bmax = s->devBBox + 3;
+			}
+			else {
+				bmin = s->host.nodes[0].bmin;
+				bmax = s->host.nodes[0].bmax;
+			}
+			float far2 = 0.0f;
+			for(int a = 0; a < 3; a++) {
+				const float ext = (bmax[a] - bmin[a]) * 0.01f;
+				const float d = std::max(std::fabs(l.pos[a] - (bmin[a] - ext)), std::fabs(l.pos[a] - (bmax[a] + ext)));
+				far2 += d * d;
+			}
+			const char *cullEnv = getenv("SNL_LIGHT_CULL");  // "0": never (ray counts then exceed the reference's; A/B)
+			if(!(far2 <= l.radSq) && !(cullEnv && cullEnv[0] == '0'))
+				S.cullMask |= 1u << i;
+		}
 		memcpy(S.lights[i].pos, l.pos, 12);
 		memcpy(S.lights[i].color, l.color, 12);
 		S.lights[i].radius = l.radius;
@@ -958,7 +985,7 @@ static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, cons
 		packets = s->dPackets.ptr;
 	}
 	const int nPk = packets ? s->nPackets : ((W + 15) / 16) * ((H + 15) / 16);
-	if(S.gvRefl && !S.gvDepth && !s->fused && !S.hasTransp && !S.gvSuper && !S.instances && nPk > 0) {
+	if(S.gvRefl && !S.gvDepth && !s->fused && !S.hasTransp && !S.gvSuper && !S.instances && !S.cullMask && nPk > 0) {
 		// reflection bounce: wavefront pipeline with queue-driven persistent traversal of the incoherent rays
 		const size_t NL = (size_t)nPk * kPacket, nl = std::max<size_t>(S.nLights, 1);
 		SNL_REQUIRE(NL * nl < 0xffffffffull, SNL_ERR_UNSUPPORTED, "frame too large for 32-bit ray ids");

@@ -788,11 +788,13 @@ __device__ __forceinline__ bool light_setup(const DevLight &L, float px, float p
 }
 
 // light_accumulate: attenuation + diffuse / specular sums of an unoccluded light (:575-598).
-__device__ __forceinline__ void light_accumulate(const DevLight &L, float dot, float distance, float &ldr, float &ldg,
-												 float &ldb, float &lsr, float &lsg, float &lsb) {
-	float atten = distance * L.iRadius;
+__device__ __forceinline__ float light_attenuation(const DevLight &L, float distance) {
+	const float atten = distance * L.iRadius;
 	const float x = ((1.0f - atten) * 0.2f + 1.0f / (16.0f * atten * atten)) - 0.0625f;
-	atten = 0.0f > x ? 0.0f : x;  // Max(f32x4(0), x)
+	return 0.0f > x ? 0.0f : x;  // Max(f32x4(0), x)
+}
+__device__ __forceinline__ void light_accumulate(const DevLight &L, float dot, float atten, float &ldr, float &ldg,
+												 float &ldb, float &lsr, float &lsg, float &lsb) {
 	const float diffMul = dot * atten;
 	float specMul = dot;
 	specMul *= specMul;
@@ -819,12 +821,18 @@ __device__ __forceinline__ bool trace_light(const SceneDev &S, int li, bool sel,
 	if(!light_setup(L, s.px, s.py, s.pz, s.nx, s.ny, s.nz, fx, fy, fz, dot, distance))
 		return false;
 	const float tmax = distance * 0.9999f;
+	// Beyond the light's radius the attenuation is exactly 0 and the ray's verdict cannot change the sums (x + 0 = x):
+	// the ray still counts as traced - the reference traces it unless the whole packet is out of range
+	// (src/scene_trace.cpp:498-499) - but the walk is skipped.
+	const float atten = light_attenuation(L, distance);
+	if(!(atten > 0.0f))
+		return true;
 	const bool occluded =
 		INST ? traverse_shadow_inst(S, L.pos[0], L.pos[1], L.pos[2], fx, fy, fz, safe_inv(fx), safe_inv(fy), safe_inv(fz), tmax, tc)
 			 : traverse_shadow(kRelNodes ? S.lightPre[li].nodes : S.nodes, S.lightPre[li].tris, L.pos[0], L.pos[1], L.pos[2], fx,
 							   fy, fz, safe_inv(fx), safe_inv(fy), safe_inv(fz), tmax, tc);
 	if(!occluded && tmax > 0.0f)
-		light_accumulate(L, dot, distance, ldr, ldg, ldb, lsr, lsg, lsb);
+		light_accumulate(L, dot, atten, ldr, ldg, ldb, lsr, lsg, lsb);
 	return true;
 }
 
@@ -844,6 +852,7 @@ __device__ __forceinline__ void reflection_ray(const Sample &s, float dx, float 
 struct PacketCounts {
 	unsigned primary, shadow, reflection, reflection_shadow, transparency;
 	int voteGen;  // packet votes taken so far (PacketVote), uniform over the CTA
+	int boxGen;   // packet hit boxes posted so far (PacketBox), uniform over the CTA
 };
 
 // selector.All() of a packet without a CTA barrier. The verdict is only consumed after the NEXT traversal (it picks
@@ -893,6 +902,126 @@ __device__ __forceinline__ bool packet_vote_all(int gen) {
 //   out = diffuse * lDiffuse + specular * lSpecular      (src/scene_trace.cpp:504-511)
 // with diffuse possibly replaced by VLerp(transColor, diffuse, opacity) once the transparency pass behind the hit has
 // returned (:468-483).
+// Warp-wide float min / max in one instruction: redux.sync.{min,max}.f32 is new with sm_100a (CREDUX.MIN/MAX.F32).
+__device__ __forceinline__ float warp_min_f32(float v) {
+	float r;
+	asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+	return r;
+}
+__device__ __forceinline__ float warp_max_f32(float v) {
+	float r;
+	asm volatile("redux.sync.max.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+	return r;
+}
+
+// The box of a packet's hit points (minPos / maxPos of Scene::RayTrace, src/scene_trace.cpp:139-140,164-165,378-379)
+// for the per-packet light cull (:494-499). Only used when a light can be out of range somewhere (SceneDev::cullMask).
+// Every warp posts its own box after the walk; the readers meet at one barrier right before the light loop. Four
+// slots: a level-0 box stays posted across the whole reflection pass, which posts and reads its own.
+struct PacketBox {
+	float v[4][kPacket / 32][6];
+};
+__device__ __forceinline__ PacketBox &packet_box_state() {
+	__shared__ PacketBox b;
+	return b;
+}
+__device__ __forceinline__ int packet_box_post(bool sel, float px, float py, float pz, PacketCounts &pc) {
+	float lo[3] = {sel ? px : CUDART_INF_F, sel ? py : CUDART_INF_F, sel ? pz : CUDART_INF_F};
+	float hi[3] = {sel ? px : -CUDART_INF_F, sel ? py : -CUDART_INF_F, sel ? pz : -CUDART_INF_F};
+#pragma unroll
+	for(int a = 0; a < 3; a++) {
+		lo[a] = warp_min_f32(lo[a]);
+		hi[a] = warp_max_f32(hi[a]);
+	}
+	const int slot = pc.boxGen++ & 3;
+	if((threadIdx.x & 31) == 0) {
+		float *d = packet_box_state().v[slot][threadIdx.x >> 5];
+		d[0] = lo[0], d[1] = lo[1], d[2] = lo[2], d[3] = hi[0], d[4] = hi[1], d[5] = hi[2];
+	}
+	return slot;
+}
+__device__ __forceinline__ void packet_box_read(int slot, float lo[3], float hi[3]) {
+	__syncthreads();
+	const PacketBox &b = packet_box_state();
+	lo[0] = lo[1] = lo[2] = CUDART_INF_F;
+	hi[0] = hi[1] = hi[2] = -CUDART_INF_F;
+	for(int w = 0; w < (int)(blockDim.x >> 5); w++)
+#pragma unroll
+		for(int a = 0; a < 3; a++) {
+			lo[a] = fminf(lo[a], b.v[slot][w][a]);
+			hi[a] = fmaxf(hi[a], b.v[slot][w][3 + a]);
+		}
+}
+// BoxPointDistanceSq (src/funcs.cpp:8-50).
+__device__ __forceinline__ float box_point_distance_sq(const float lo[3], const float hi[3], const float p[3]) {
+	float sq = 0.0f;
+#pragma unroll
+	for(int a = 0; a < 3; a++) {
+		if(p[a] < lo[a]) {
+			const float d = p[a] - lo[a];
+			sq += d * d;
+		}
+		else if(p[a] > hi[a]) {
+			const float d = p[a] - hi[a];
+			sq += d * d;
+		}
+	}
+	return sq;
+}
+
+// Deferred form of the cull for the plain k_render (FLAGS bit 4): no barrier inside the frame. Lanes skip the walk on
+// their own where the attenuation is 0 (trace_light), shadow rays of cullable lights are counted per (level, light)
+// in shared memory, every warp leaves its level boxes there, and cull_resolve() at the end of the kernel keeps the
+// counts of the (level, light) pairs the reference would have traced. cull_state_init() + barrier at kernel start.
+struct CullState {
+	float box[2][kPacket / 32][6];
+	unsigned cnt[2][kMaxLights];
+};
+__device__ __forceinline__ CullState &cull_state() {
+	__shared__ CullState c;
+	return c;
+}
+__device__ __forceinline__ void cull_state_init() {
+	if(threadIdx.x < 2 * kMaxLights)
+		(&cull_state().cnt[0][0])[threadIdx.x] = 0;
+}
+__device__ __forceinline__ void cull_box_store(int level, bool sel, float px, float py, float pz) {
+	float lo[3] = {sel ? px : CUDART_INF_F, sel ? py : CUDART_INF_F, sel ? pz : CUDART_INF_F};
+	float hi[3] = {sel ? px : -CUDART_INF_F, sel ? py : -CUDART_INF_F, sel ? pz : -CUDART_INF_F};
+#pragma unroll
+	for(int a = 0; a < 3; a++) {
+		lo[a] = warp_min_f32(lo[a]);
+		hi[a] = warp_max_f32(hi[a]);
+	}
+	if((threadIdx.x & 31) == 0) {
+		float *d = cull_state().box[level][threadIdx.x >> 5];
+		d[0] = lo[0], d[1] = lo[1], d[2] = lo[2], d[3] = hi[0], d[4] = hi[1], d[5] = hi[2];
+	}
+}
+__device__ __forceinline__ void cull_resolve(const SceneDev &S, PacketCounts &pc) {
+	__syncthreads();
+	if((int)threadIdx.x >= 2 * S.nLights)
+		return;
+	const int level = (int)threadIdx.x / S.nLights, li = (int)threadIdx.x % S.nLights;
+	const CullState &c = cull_state();
+	const unsigned n = c.cnt[level][li];
+	if(!n)
+		return;
+	float lo[3] = {CUDART_INF_F, CUDART_INF_F, CUDART_INF_F}, hi[3] = {-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F};
+	for(int w = 0; w < (int)(blockDim.x >> 5); w++)
+#pragma unroll
+		for(int a = 0; a < 3; a++) {
+			lo[a] = fminf(lo[a], c.box[level][w][a]);
+			hi[a] = fmaxf(hi[a], c.box[level][w][3 + a]);
+		}
+	if(box_point_distance_sq(lo, hi, S.lights[li].pos) > S.lights[li].radSq)
+		return;
+	if(level == 0)
+		pc.shadow += n;
+	else
+		pc.reflection_shadow += n;
+}
+
 struct LevelOut {
 	float ar, ag, ab;  // samples.diffuse after the reflection blend
 	float lr, lg, lb;  // lDiffuse
@@ -971,6 +1100,14 @@ __device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet o
 	// maskGen > 0: "ask packet vote maskGen" (posted by the level above before this level's traversal)
 	const bool packetHasMask = maskGen > 0 ? !packet_vote_all(maskGen) : maskGen != 0;
 	shade_block<TRANSP, INST>(S, sel, h, ox, oy, oz, dx, dy, dz, packetHasMask, s, trans);
+	constexpr bool DEFER = (FLAGS & 4) != 0;  // light-cull accounting at the end of the kernel (cull_resolve)
+	int boxSlot = 0;
+	if(S.cullMask) {
+		if(DEFER)
+			cull_box_store(LEVEL, sel, s.px, s.py, s.pz);
+		else
+			boxSlot = packet_box_post(sel, s.px, s.py, s.pz, pc);
+	}
 
 	if(LEVEL == 0 && S.gvRefl) {  // src/scene_trace.cpp:454-466, TraceReflection :603-618
 		// selector.All() of the packet (src/scene_trace.cpp:615-617) picks RayGroup<0,0> or <0,1> for the bounce; only
@@ -994,9 +1131,21 @@ __device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet o
 	if(S.nLights) {
 		float ldr = S.ambient[0], ldg = S.ambient[1], ldb = S.ambient[2];
 		float lsr = 0.0f, lsg = 0.0f, lsb = 0.0f;
+		float boxLo[3], boxHi[3];
+		if(S.cullMask && !DEFER)
+			packet_box_read(boxSlot, boxLo, boxHi);
 		for(int li = 0; li < S.nLights; li++) {
+			const bool cullable = (S.cullMask >> li & 1) != 0;
+			// the packet's hit points are all farther from this light than its radius: src/scene_trace.cpp:498-499
+			if(!DEFER && cullable && box_point_distance_sq(boxLo, boxHi, S.lights[li].pos) > S.lights[li].radSq)
+				continue;
 			const bool cast = trace_light<INST>(S, li, sel, s, ldr, ldg, ldb, lsr, lsg, lsb, tc);
-			if(cast) {
+			if(DEFER && cullable) {
+				const unsigned m = __ballot_sync(SNL_FULL, cast);
+				if((threadIdx.x & 31) == 0 && m)
+					atomicAdd(&cull_state().cnt[LEVEL][li], (unsigned)__popc(m));
+			}
+			else if(cast) {
 				if(LEVEL == 0)
 					pc.shadow++;
 				else

@@ -212,6 +212,12 @@ __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreS
 	const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
 	PacketCounts pc = {0, 0, 0, 0, 0};
 	TravCount tc = {0, 0, 0};
+	// the plain kernel settles the per-packet light cull's ray accounting at its end instead of with barriers per level
+	constexpr int LFLAGS = (FLAGS == 0 && !SUPER) ? 4 : FLAGS;
+	if(LFLAGS == 4 && S.cullMask) {
+		cull_state_init();
+		__syncthreads();
+	}
 	if(S.hasUber)
 		packet_vote_init();
 	// Like the reference we trace the whole 16x16 packet even when it overhangs the image or the tile
@@ -225,7 +231,7 @@ __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreS
 		else
 			gen_primary(g, px0, py0, tx, ty, dx, dy, dz);
 		float r = 0.0f, gg = 0.0f, b = 0.0f;
-		raytrace_lane<0, true, FLAGS>(S, pre, active, 0, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, r, gg, b, pc, tc);
+		raytrace_lane<0, true, LFLAGS>(S, pre, active, 0, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, r, gg, b, pc, tc);
 		int ox = tx, oy = ty;
 		bool store = true;
 		if(SUPER) {
@@ -254,6 +260,8 @@ __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreS
 		}
 		__syncwarp();
 	}
+	if(LFLAGS == 4 && S.cullMask)
+		cull_resolve(S, pc);
 	flush_counts(S, pc, tc);
 }
 

@@ -351,7 +351,7 @@ __global__ void __launch_bounds__(kPacket) k_wf_resolve(SceneDev S, WfBuffers B,
 				const float2 dd = B.sdot[li * B.NL + id];
 				// cast (N.L > 0), not occluded, tmax > 0
 				if(dd.x > 0.0f && !((occl >> li) & 1) && dd.y * 0.9999f > 0.0f)
-					light_accumulate(S.lights[li], dd.x, dd.y, ldr, ldg, ldb, lsr, lsg, lsb);
+					light_accumulate(S.lights[li], dd.x, light_attenuation(S.lights[li], dd.y), ldr, ldg, ldb, lsr, lsg, lsb);
 			}
 			cr = d1.x * ldr + s1.x * lsr;
 			cg = d1.y * ldg + s1.y * lsg;

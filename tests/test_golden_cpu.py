@@ -15,7 +15,7 @@ MANIFEST = json.load(open(os.path.join(GOLDEN, "manifest.json")))
 CASES = list(MANIFEST["cases"])
 STAGES = {"simple_nolight": ({}, False), "depth": ({1: 1}, False), "simple_light": ({}, True),
           "full_light": ({6: 1}, True), "whitted": ({6: 1, 7: 1}, True),
-          "whitted_ss": ({6: 1, 7: 1, 9: 1}, True)}
+          "whitted_ss": ({6: 1, 7: 1, 9: 1}, True), "whitted_3l": ({6: 1, 7: 1}, 3)}
 
 
 def golden(name):
@@ -47,7 +47,7 @@ def test_oracle_reproduces_goldens(name):
     assert (ref.primary_dirs(g["camera"], W, H) == g["dirs"]).all()
     for stage, (gv, lit) in STAGES.items():
         ref.set_gvals(gv)
-        ref.set_lights([g["light"]] if lit else [])
+        ref.set_lights(list(g["lights3"]) if lit == 3 else [g["light"]] if lit else [])
         img, st, _ = ref.render(g["camera"], W, H, threads=2)
         ok = (img == g["img_" + stage]).all(axis=2)
         undef = g["undef_" + stage] if stage != "depth" else g["undef_simple"]

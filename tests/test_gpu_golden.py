@@ -14,7 +14,7 @@ pytestmark = pytest.mark.gpu
 MANIFEST = json.load(open(os.path.join(GOLDEN, "manifest.json")))
 STAGES = {"simple_nolight": ({}, False), "depth": ({1: 1}, False), "simple_light": ({}, True),
           "full_light": ({6: 1}, True), "whitted": ({6: 1, 7: 1}, True),
-          "whitted_ss": ({6: 1, 7: 1, 9: 1}, True)}
+          "whitted_ss": ({6: 1, 7: 1, 9: 1}, True), "whitted_3l": ({6: 1, 7: 1}, 3)}
 T_REL = 1e-5
 
 
@@ -69,7 +69,7 @@ def test_render_stages_vs_golden(sb, name):
     light = sb.Light(lg[0:3], lg[3:6], lg[6])
     for stage, (gv, lit) in STAGES.items():
         sc.set_options(gv)
-        sc.set_lights([light] if lit else [])
+        sc.set_lights([sb.Light(l[0:3], l[3:6], l[6]) for l in g["lights3"]] if lit == 3 else [light] if lit else [])
         img, st = sc.render(cam, W, H)
         err = np.abs(img.astype(np.int16) - g["img_" + stage].astype(np.int16)).max(axis=2)
         undef = g["undef_" + stage] if stage != "depth" else g["undef_simple"]

@@ -12,7 +12,7 @@ from conftest import DATA, GOLDEN, ROOT
 MANIFEST = json.load(open(os.path.join(GOLDEN, "manifest.json")))
 STAGES = {"simple_nolight": ({}, False), "depth": ({1: 1}, False), "simple_light": ({}, True),
           "full_light": ({6: 1}, True), "whitted": ({6: 1, 7: 1}, True),
-          "whitted_ss": ({6: 1, 7: 1, 9: 1}, True)}
+          "whitted_ss": ({6: 1, 7: 1, 9: 1}, True), "whitted_3l": ({6: 1, 7: 1}, 3)}
 
 
 def find(sub, name):
@@ -68,7 +68,7 @@ def test_c_oracle_frames_vs_golden(sb, name):
     W, H = int(g["size"][0]), int(g["size"][1])
     for stage, (gv, lit) in STAGES.items():
         orc.set_gvals(gv)
-        orc.set_lights([g["light"]] if lit else [])
+        orc.set_lights(list(g["lights3"]) if lit == 3 else [g["light"]] if lit else [])
         img, st = orc.render(g["camera"], W, H)
         err = np.abs(img.astype(np.int16) - g["img_" + stage].astype(np.int16)).max(axis=2)
         undef = g["undef_" + stage] if stage != "depth" else g["undef_simple"]

@@ -41,7 +41,18 @@ STAGES = {
     "full_light": ({6: 1}, True),
     "whitted": ({6: 1, 7: 1}, True),
     "whitted_ss": ({6: 1, 7: 1, 9: 1}, True),  # + 2x2 supersampling (src/render.cpp:71-110)
+    "whitted_3l": ({6: 1, 7: 1}, 3),  # three lights (out["lights3"]): colours, a radius that leaves part of the scene dark
 }
+
+
+def three_lights(light, bmin, bmax):
+    """The case's light plus two coloured ones offset from it (they stay inside the closed test rooms); the second has a
+    radius shorter than the scene, so TraceLight's attenuation reaches zero inside the frame (src/scene_trace.cpp:575-585)."""
+    S = np.float32(np.linalg.norm(np.asarray(bmax, np.float32) - np.asarray(bmin, np.float32)))
+    p = np.asarray(light[:3], np.float32)
+    l1 = np.array([*(p + np.float32([0.15, 0.10, 0.05]) * S), 1.0, 0.25, 0.1, 0.45 * S], np.float32)
+    l2 = np.array([*(p + np.float32([-0.20, -0.05, 0.10]) * S), 0.1, 0.3, 1.0, float(light[6])], np.float32)
+    return np.stack([np.asarray(light, np.float32), l1, l2])
 
 # name -> (obj, mtl, inside camera, W, H)
 CASES = {
@@ -231,15 +242,17 @@ def main():
         hn, ht, hsh, hm = hs.bvh()
         orc = O.OracleScene(hn, ht, hsh, hm, hs.materials(), hs.textures())
         rays = {}
+        out["lights3"] = three_lights(light, bmin, bmax)
         for stage, (gv, lit) in STAGES.items():
+            lights = list(out["lights3"]) if lit == 3 else [light] if lit else []
             ref.set_gvals(gv)
-            ref.set_lights([light] if lit else [])
+            ref.set_lights(lights)
             img, st, _ = ref.render(cam, W, H, threads=1)
             out["img_" + stage] = img
             rays[stage] = st["rays"]
             if stage != "depth":
                 orc.set_gvals(gv)
-                orc.set_lights([light] if lit else [])
+                orc.set_lights(lights)
                 u = np.zeros((H, W), np.uint8)
                 orc.render(cam, W, H, undef=u)
                 out["undef_" + stage] = (u != 0) | (out["undef_ss"] if stage.endswith("_ss") else out["undef_simple"])
