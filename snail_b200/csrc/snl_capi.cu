@@ -144,10 +144,14 @@ struct Flattener {
 };
 
 int sync_and_stats(snl_scene *s, snl_stats *stats) {
+	if(stats) {
+		if(!s->hCounters)
+			SNL_CUDA(cudaMallocHost(&s->hCounters, sizeof(Counters)));
+		SNL_CUDA(cudaMemcpyAsync(s->hCounters, s->dCounters.ptr, sizeof(Counters), cudaMemcpyDeviceToHost, s->stream));
+	}
 	SNL_CUDA(cudaStreamSynchronize(s->stream));
 	if(stats) {
-		Counters c;
-		SNL_CUDA(cudaMemcpy(&c, s->dCounters.ptr, sizeof(c), cudaMemcpyDeviceToHost));
+		const Counters c = *s->hCounters;
 		memset(stats, 0, sizeof(*stats));
 		stats->primary = c.primary;
 		stats->shadow = c.shadow;
@@ -160,8 +164,10 @@ int sync_and_stats(snl_scene *s, snl_stats *stats) {
 		stats->gtri_tests = c.gtri_tests;
 		if(s->evPending) {
 			float ms = 0.0f;
-			if(cudaEventElapsedTime(&ms, s->ev0, s->ev1) == cudaSuccess)
+			if(cudaEventElapsedTime(&ms, s->ev0, s->ev1) == cudaSuccess) {
 				stats->kernel_ms = ms;
+				s->lastCallMs = ms;
+			}
 		}
 	}
 	s->evPending = false;
@@ -389,7 +395,9 @@ void snl_scene_destroy(snl_scene *s) {
 		cudaEventDestroy(s->ev1);
 	if(s->forkEv)
 		cudaEventDestroy(s->forkEv);
-	for(int b = 0; b < snl_scene::kBands; b++) {
+	if(s->hCounters)
+		cudaFreeHost(s->hCounters);
+	for(int b = 0; b < snl_scene::kMaxBands; b++) {
 		if(s->bandEv[b])
 			cudaEventDestroy(s->bandEv[b]);
 		if(s->bandStream[b])
@@ -1063,19 +1071,23 @@ static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, cons
 		SNL_CUDA(cudaEventRecord(s->ev0, s->stream));
 	}
 	const int variant = T.choice;
-	const char *bandsEnv = getenv("SNL_RENDER_BANDS");  // "0": one launch, copy afterwards
-	if(hostOut && hostDone && !packets && nPk >= 8 * s->smCount && !(bandsEnv && bandsEnv[0] == '0')) {
+	const char *bandsEnv = getenv("SNL_RENDER_BANDS");  // number of bands; "0" / "1": one launch, copy afterwards
+	// frames of a millisecond and more hide more of the copy with eight bands (+1.2 % e2e on sponza_like); short ones lose
+	// more to the extra launches than they gain (-1 % on feline): four
+	const int nBands = bandsEnv ? std::min(atoi(bandsEnv), (int)snl_scene::kMaxBands)
+								: (s->lastCallMs > 0.8f ? (int)snl_scene::kMaxBands : (int)snl_scene::kBands);
+	if(hostOut && hostDone && !packets && nPk >= 8 * s->smCount && nBands > 1) {
 		if(!s->forkEv) {
 			SNL_CUDA(cudaEventCreateWithFlags(&s->forkEv, cudaEventDisableTiming));
-			for(int b = 0; b < snl_scene::kBands; b++) {
+			for(int b = 0; b < snl_scene::kMaxBands; b++) {
 				SNL_CUDA(cudaStreamCreateWithFlags(&s->bandStream[b], cudaStreamNonBlocking));
 				SNL_CUDA(cudaEventCreateWithFlags(&s->bandEv[b], cudaEventDisableTiming));
 			}
 		}
 		const int px = (W + 15) / 16, py = (H + 15) / 16;
 		SNL_CUDA(cudaEventRecord(s->forkEv, s->stream));
-		for(int b = 0; b < snl_scene::kBands; b++) {
-			const int r0 = py * b / snl_scene::kBands, r1 = py * (b + 1) / snl_scene::kBands;
+		for(int b = 0; b < nBands; b++) {
+			const int r0 = py * b / nBands, r1 = py * (b + 1) / nBands;
 			if(r1 <= r0)
 				continue;
 			cudaStream_t st = s->bandStream[b];

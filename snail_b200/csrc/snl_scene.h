@@ -59,9 +59,11 @@ struct snl_scene {
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 	// snl_render to a host image: the frame is rendered as kBands row bands on their own streams, each followed by the
 	// device->host copy of its rows, so all but the last band's copy overlaps the rendering of the bands after it
-	enum { kBands = 4 };
-	cudaStream_t bandStream[kBands] = {nullptr, nullptr, nullptr, nullptr};
-	cudaEvent_t bandEv[kBands] = {nullptr, nullptr, nullptr, nullptr}, forkEv = nullptr;
+	enum { kBands = 4, kMaxBands = 8 };  // default / most bands (SNL_RENDER_BANDS=n)
+	cudaStream_t bandStream[kMaxBands] = {};
+	cudaEvent_t bandEv[kMaxBands] = {}, forkEv = nullptr;
+	float lastCallMs = 0.0f;             // device time of the last call that asked for stats (picks the band count)
+	snl::Counters *hCounters = nullptr;  // pinned: the counters travel back in-stream, one synchronisation per call
 	bool evPending = false;
 
 	// k_render comes in two register budgets (snl_kernels.cu, MINB); the first frame of a workload is rendered with
