@@ -153,7 +153,7 @@ def run_reference(args, w, W, H):
         "e2e": {"value": round(val, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "wall_s": round(wall, 2),
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=JSON_OUT, flush=True)
 
 
 def algorithmic_bytes(sb, w, W, H, cam, light):
@@ -384,13 +384,22 @@ def run_ours(args, w, W, H):
                                 "cpu_utilisation": round(util, 2),
                                 "sample": f"{frames} full {W}x{H} frames of the same workload through the reference's "
                                           f"Render() (oracle/_ref, veclib {variant}), {threads} threads"}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=JSON_OUT, flush=True)
     sc.close()
     if dist:
         dist.destroy_process_group()
 
 
+JSON_OUT = sys.stdout
+
+
 def main():
+    # stdout carries ONE JSON line: anything native code prints there (the reference's loader reports "Done loading"
+    # through C stdio, flushed whenever) is sent to stderr instead
+    global JSON_OUT
+    sys.stdout.flush()
+    JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     args = parse_args()
     from snail_b200 import workloads
     w = workloads.resolve(args.workload)
