@@ -38,6 +38,7 @@ def parse_args():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD)
     ap.add_argument("--res", default="1920x1080")
     ap.add_argument("--compose", default="p2p", choices=["p2p", "nccl"])
+    ap.add_argument("--tile", default="16x64", help="farm tile size for N > 1 (the reference's blockWidth x blockHeight)")
     ap.add_argument("--sustain", type=float, default=1.0, help="seconds of back-to-back replay for clock sampling")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
@@ -204,7 +205,8 @@ def run_ours(args, w, W, H):
     bmin, bmax = sc.bbox()
     stream = torch.cuda.ExternalStream(sc.stream(), device=dev)
     pitch = W * 3
-    tiles = farm.tiles_for_rank(W, H, rank, world) if world > 1 else None
+    tbw, tbh = [int(x) for x in args.tile.lower().split("x")]
+    tiles = farm.tiles_for_rank(W, H, rank, world, bw=tbw, bh=tbh) if world > 1 else None
 
     # The frame lives in rank 0's HBM. "p2p": the other ranks map it (CUDA IPC) and k_render stores into it over
     # NVLink. "nccl": every rank renders into a local frame and the tiles are gathered with torch.distributed.
@@ -340,7 +342,7 @@ def run_ours(args, w, W, H):
                    "l2": "256 MiB buffer written between timed steps (L2 flush)",
                    "timing": "CUDA events on the scene stream around each step (barrier + sync on both sides), "
                              "per-step max over ranks, summed",
-                   "compose": compose, "tiles": "16x64, shuffled per group of N ranks" if world > 1 else "full frame"},
+                   "compose": compose, "tiles": f"{args.tile}, shuffled per group of N ranks" if world > 1 else "full frame"},
         "gpu_launches": int(launches), "clocks": clocks, "wall_s": round(wall, 3),
         "sustained": {"value": round(sus_value, 2), "unit": UNIT, "frames": sus_frames,
                       "note": "same step replayed back to back, no L2 flush, no per-step sync, camera fixed"},

@@ -42,8 +42,8 @@ def assign_tiles(n_tiles: int, world: int, seed: int = 1) -> np.ndarray:
     return out
 
 
-def tiles_for_rank(W: int, H: int, rank: int, world: int, seed: int = 1) -> np.ndarray:
-    tiles = divide_image(W, H)
+def tiles_for_rank(W: int, H: int, rank: int, world: int, seed: int = 1, bw: int = BLOCK_W, bh: int = BLOCK_H) -> np.ndarray:
+    tiles = divide_image(W, H, bw, bh)
     if world == 1:
         return tiles
     return tiles[assign_tiles(len(tiles), world, seed) == rank]
