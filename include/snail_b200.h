@@ -244,6 +244,22 @@ int snl_frame_open(snl_scene *, const unsigned char ipc_handle[SNL_IPC_HANDLE_BY
 int snl_frame_close(snl_scene *, void *bgr8_dev); /* frees (owner) or unmaps (peer) */
 int snl_frame_read(snl_scene *, const void *bgr8_dev, int W, int H, unsigned char *bgr8_host, size_t host_pitch);
 
+/* Builder-side ceilings for the roofline of the traversal kernels (bench.py `roofline`): the reference's scenes are
+ * L2-resident on a B200 and the walk is served by L1, so what bounds k_render is instruction issue and L1 / L2
+ * bandwidth, not HBM. Streaming microbenchmarks timed with CUDA events on `device` (snail_b200/csrc/snl_peaks.cu);
+ * allocates 2 GiB for a second. Replaces nothing in the reference (its analogue is the `it:` / `in:` statistics of
+ * src/tree_stats.cpp:35-36). */
+typedef struct snl_peaks {
+	float l1_gbs;                 /* L1 -> SM, coalesced 128-bit loads of an L1-resident window, all SMs */
+	float l2_gbs;                 /* L2 -> SM, 48 MB streamed with L1 bypassed */
+	float hbm_read_gbs;           /* HBM -> SM, 2 GiB read once */
+	float issue_gwarpinst_s;      /* measured: FFMA + integer ALU interleave, 1e9 warp instructions / s */
+	float issue_peak_gwarpinst_s; /* SMs x 4 schedulers x max SM clock */
+	float sm_clock_mhz_max;
+	int sms;
+} snl_peaks;
+int snl_measure_peaks(int device, snl_peaks *out);
+
 /* Number of kernels this library launched on the scene since creation (bench.py's gpu_launches). */
 uint64_t snl_scene_launch_count(snl_scene *);
 

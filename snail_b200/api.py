@@ -24,6 +24,7 @@ ABI_SYMBOLS = [
     "snl_host_scene_counts", "snl_host_scene_copy", "snl_host_scene_material", "snl_host_scene_texture",
     "snl_scene_set_host_scene", "snl_scene_build_device", "snl_scene_build_ms", "snl_scene_set_instances",
     "snl_trace_primary_inst", "snl_scene_copy_dbvh", "snl_host_dbvh_build", "snl_frame_create", "snl_frame_open", "snl_frame_close", "snl_frame_read",
+    "snl_measure_peaks",
 ]
 
 # reference record layouts (src/bvh/tree.h:60-72, src/triangle.h:133-135,181-230)
@@ -96,6 +97,11 @@ class Stats(C.Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class Peaks(C.Structure):
+    _fields_ = [("l1_gbs", C.c_float), ("l2_gbs", C.c_float), ("hbm_read_gbs", C.c_float), ("issue_gwarpinst_s", C.c_float),
+                ("issue_peak_gwarpinst_s", C.c_float), ("sm_clock_mhz_max", C.c_float), ("sms", C.c_int)]
+
+
 _libs: dict[str, C.CDLL] = {}
 
 
@@ -152,12 +158,23 @@ def load_library(counters: bool = False) -> C.CDLL:
     L.snl_frame_open.argtypes = [vp, C.c_char_p, C.POINTER(C.c_void_p)]
     L.snl_frame_close.argtypes = [vp, vp]
     L.snl_frame_read.argtypes = [vp, vp, i, i, vp, C.c_size_t]
+    L.snl_measure_peaks.argtypes = [i, C.POINTER(Peaks)]
     _libs[path] = L
     return L
 
 
 def _ptr(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def measure_peaks(device: int = 0) -> dict:
+    """Builder-measured L1 / L2 / HBM-read bandwidth and issue rate of `device` (snl_measure_peaks)."""
+    L = load_library()
+    p = Peaks()
+    r = L.snl_measure_peaks(device, C.byref(p))
+    if r:
+        raise SnlError(r, L.snl_last_error().decode())
+    return {n: getattr(p, n) for n, _ in p._fields_}
 
 
 def host_dbvh_build(instances, tree_min, tree_max):

@@ -14,7 +14,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libsnail_b200.so")
 LIB_COUNTERS = os.path.join(HERE, "libsnail_b200_counters.so")
 
-SOURCES = ["snl_kernels.cu", "snl_wavefront.cu", "snl_build.cu", "snl_capi.cu", "snl_host_scene.cpp", "snl_host_dbvh.cpp"]
+SOURCES = ["snl_kernels.cu", "snl_wavefront.cu", "snl_build.cu", "snl_capi.cu", "snl_peaks.cu", "snl_host_scene.cpp", "snl_host_dbvh.cpp"]
 HEADERS = ["snl_device.cuh", "snl_kernels.h", "snl_scene.h", "snl_scene_dev.h", "snl_types.h", "snl_host_scene.h",
            os.path.join("..", "..", "include", "snail_b200.h")]
 
@@ -47,6 +47,8 @@ def build_library(force: bool = False, counters: bool = False, verbose: bool = F
     if not force and not _stale(target):
         return target
     flags = [f for f in NVCC_FLAGS if f != "--use_fast_math=false"]
+    if "-fmad=true" in extra:  # A/B only: contracts a*b+c everywhere, t / u / v are no longer bit-identical with the reference
+        flags = [f for f in flags if f != "-fmad=false"]
     if counters:
         flags += ["-DSNL_COUNTERS"]
     flags += list(extra)
@@ -64,7 +66,7 @@ def build_library(force: bool = False, counters: bool = False, verbose: bool = F
 
 
 if __name__ == "__main__":
-    extra = [a for a in sys.argv[1:] if a.startswith("-D") or a.startswith("-maxrregcount")]
+    extra = [a for a in sys.argv[1:] if a.startswith("-D") or a.startswith("-maxrregcount") or a == "-fmad=true"]
     suffix = next((a.split("=", 1)[1] for a in sys.argv[1:] if a.startswith("--suffix=")), "")
     path = build_library(force="--force" in sys.argv, counters="--counters" in sys.argv, verbose="-v" in sys.argv,
                          extra=extra, suffix=suffix)

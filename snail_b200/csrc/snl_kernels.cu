@@ -212,6 +212,8 @@ __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreS
 	const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
 	PacketCounts pc = {0, 0, 0, 0, 0};
 	TravCount tc = {0, 0, 0};
+	constexpr bool VSTORE = !SUPER;
+	__shared__ __align__(16) unsigned char tile[VSTORE ? 16 * 48 : 16];
 	// the plain kernel settles the per-packet light cull's ray accounting at its end instead of with barriers per level
 	constexpr int LFLAGS = (FLAGS == 0 && !SUPER) ? 4 : FLAGS;
 	if(LFLAGS == 4 && S.cullMask) {
@@ -252,17 +254,38 @@ __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreS
 			gg = (gg + 0.1f) * S.tint[1];
 			b = (b + 0.1f) * S.tint[2];
 		}
-		if(store && ox < cw && oy < ch) {
+		const unsigned cb = conv_channel(b), cg = conv_channel(gg), cr = conv_channel(r);
+		if(VSTORE) {
+			// stage the packet's 16 x 48 bytes and write them as 16-byte vectors below: one 16-byte store per 5.3 pixels
+			// instead of three 1-byte stores per pixel (what matters when `out` is rank 0's frame behind NVLink)
+			unsigned char *t = tile + ty * 48 + tx * 3;
+			t[0] = (unsigned char)cb;
+			t[1] = (unsigned char)cg;
+			t[2] = (unsigned char)cr;
+		}
+		else if(store && ox < cw && oy < ch) {
 			unsigned char *dst = out + (size_t)(py0 + oy) * pitch + (size_t)(px0 + ox) * 3;
-			dst[0] = (unsigned char)conv_channel(b);
-			dst[1] = (unsigned char)conv_channel(gg);
-			dst[2] = (unsigned char)conv_channel(r);
+			dst[0] = (unsigned char)cb;
+			dst[1] = (unsigned char)cg;
+			dst[2] = (unsigned char)cr;
 		}
 		__syncwarp();
 	}
 	if(LFLAGS == 4 && S.cullMask)
 		cull_resolve(S, pc);
-	flush_counts(S, pc, tc);
+	flush_counts(S, pc, tc);  // its barriers also publish `tile`
+	if(VSTORE && threadIdx.x < 48) {
+		const int row = threadIdx.x / 3, part = threadIdx.x - row * 3;  // 3 x 16 bytes per packet row
+		if(row < ch) {
+			unsigned char *dst = out + (size_t)(py0 + row) * pitch + (size_t)px0 * 3 + part * 16;
+			const unsigned char *src = tile + row * 48 + part * 16;
+			if(cw == 16 && !((size_t)dst & 15))
+				*reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(src);
+			else
+				for(int i = 0; i < 16 && part * 16 + i < cw * 3; i++)
+					dst[i] = src[i];
+		}
+	}
 }
 
 // ---- launch wrappers ------------------------------------------------------------------------------------------
