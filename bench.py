@@ -38,10 +38,10 @@ def parse_args():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD)
     ap.add_argument("--res", default="1920x1080")
     ap.add_argument("--compose", default="p2p", choices=["p2p", "nccl"])
-    ap.add_argument("--tile", default="16x64", help="farm tile size for N > 1 (the reference's blockWidth x blockHeight)")
     ap.add_argument("--sustain", type=float, default=1.0, help="seconds of back-to-back replay for clock sampling")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--ncu-child", action="store_true", help="internal: the frames ncu profiles for the roofline")
     return ap.parse_args()
 
 
@@ -157,32 +157,145 @@ def run_reference(args, w, W, H):
     print(json.dumps(line), file=JSON_OUT, flush=True)
 
 
-def algorithmic_bytes(sb, w, W, H, cam, light):
-    """B = 64 B x inner nodes fetched + 48 B x per-origin triangle records tested + 64 B x general
-    triangle records tested + 16 B hit record per ray + 64 B ShTriangle per shaded hit + 3 B per pixel, counted by
-    the SAME kernels built with -DSNL_COUNTERS (single-ray, near-child-first walk). One untimed frame."""
+NCU_METRICS = ["smsp__inst_executed.sum", "smsp__thread_inst_executed.sum", "l1tex__t_bytes.sum",
+               "l1tex__data_pipe_lsu_wavefronts.sum", "lts__t_bytes.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+               "smsp__issue_active.avg.pct_of_peak_sustained_active", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
+               "lts__throughput.avg.pct_of_peak_sustained_elapsed", "launch__registers_per_thread", "gpu__time_duration.sum"]
+
+
+def walker_counts(name, W, H):
+    """Nodes visited / triangles tested by a SINGLE-RAY walk of the reference's tree (near child first, early out on
+    lmin > t_best) for this workload's frame: the oracle's instrumented walker, run once where the oracle lives and
+    committed next to the goldens (tools/make_walker_counts.py -> tests/golden/walker_counts.json). Data, not code: the
+    bench never executes the oracle on this path."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "tests", "golden", "walker_counts.json")))
+        return t.get(f"{name}@{W}x{H}")
+    except Exception:
+        return None
+
+
+def counters_build_counts(sb, w, W, H, cam, light):
+    """Fallback for workloads without committed walker counts: the same kernels built with -DSNL_COUNTERS."""
     if not os.path.exists(sb.api.LIB_COUNTERS_PATH):
-        return None, None
+        return None
     sc = sb.Scene(0, counters=True)
     sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"])
     sc.set_options(w["gvals"])
     sc.set_lights([light] if w["lit"] else [])
     _, st = sc.render(cam, W, H)
     sc.close()
-    shaded = st["reflection"] + st["reflection"]  # upper bound on shaded hits: primary hits + reflected hits
-    b = (64 * st["node_visits"] + 48 * st["tri_tests"] + 64 * st["gtri_tests"] + 16 * st["rays"] + 64 * shaded + 3 * W * H)
-    return b, st
+    return {"box_tests": 2 * st["node_visits"], "tri_tests": st["tri_tests"] + st["gtri_tests"], "rays": st["rays"],
+            "shaded_hits": st["reflection"] + st["reflection"], "source": "snail_b200 kernels built with -DSNL_COUNTERS"}
 
 
-def load_traffic(name, W, H):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one k_render launch from the committed ncu --set full capture
-    of this workload (profiles/traffic.json, written by hand from the .ncu-rep summary), or None."""
+def ncu_child(args, w, W, H):
+    """`bench.py --ncu-child` (run under ncu by ncu_pass): three device-resident frames of the workload at the bench
+    camera with the kept register-budget variant pinned; ncu profiles the third k_render launch."""
+    import snail_b200 as sb
+    sc = sb.Scene(0)
+    sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"])
+    sc.set_options(w["gvals"])
+    bmin, bmax = sc.bbox()
+    frame, _ = sc.frame_create(W, H)
+    for i in range(3):
+        cam, light = camera_for_step(sb, bmin, bmax, w["inside"], args.warmup)
+        sc.set_lights([light] if w["lit"] else [])
+        sc.render_dev(cam, W, H, frame, W * 3)
+        sc.sync()
+    sc.close()
+
+
+def ncu_pass(args, W, H, variant):
+    """Counters of ONE k_render launch of this workload, collected by ncu in a child process after the timed region
+    (nothing here is a timing: instruction / byte / wavefront counts and utilisation ratios only)."""
+    import csv
+    import shutil
+    ncu = shutil.which("ncu") or "/usr/local/cuda/bin/ncu"
+    if not os.path.exists(ncu):
+        return None, "ncu not found"
+    env = dict(os.environ, SNL_RENDER_VARIANT=str(max(0, variant)), CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", "0"))
+    cmd = [ncu, "--metrics", ",".join(NCU_METRICS), "--clock-control", "none", "-k", "regex:k_render", "--launch-skip", "2",
+           "--launch-count", "1", "--csv", sys.executable, os.path.abspath(__file__), "--ncu-child", "--workload", args.workload,
+           "--res", args.res, "--warmup", str(args.warmup)]
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        e = t.get(f"{name}@{W}x{H}")
-        return (int(e["dram_bytes_per_launch"]), e["source"], e.get("ncu")) if e else (None, None, None)
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=420, env=env)
+    except Exception as e:  # noqa: BLE001
+        return None, f"ncu failed: {e}"
+    rows = [row for row in csv.reader(r.stdout.splitlines()) if len(row) > 5]
+    hdr = next((row for row in rows if "Metric Name" in row), None)
+    if hdr is None:
+        return None, "ncu gave no metrics: " + (r.stderr or r.stdout)[-300:].replace("\n", " ")
+    iN, iV, iK = hdr.index("Metric Name"), hdr.index("Metric Value"), hdr.index("Kernel Name")
+    out = {"kernel": None}
+    for row in rows:
+        if row is hdr or len(row) <= max(iN, iV):
+            continue
+        try:
+            out[row[iN]] = float(row[iV].replace(",", ""))
+            out["kernel"] = row[iK]
+        except ValueError:
+            pass
+    return (out, None) if "smsp__inst_executed.sum" in out else (None, "ncu output lacks smsp__inst_executed.sum")
+
+
+def build_roofline(sb, args, w, W, H, sc, ms_per_launch, clocks, rank):
+    """What bounds k_render (the scene is L2-resident, the walk is served by L1): instruction issue first, then L1
+    wavefronts; HBM is idle. Peaks are measured in this run (snl_measure_peaks), counts come from an ncu pass of the same
+    frame, the algorithmic figure from the oracle's single-ray walker."""
+    bmin, bmax = sc.bbox()
+    cam, light = camera_for_step(sb, bmin, bmax, w["inside"], args.warmup)
+    t = ms_per_launch * 1e-3
+    peaks = sb.measure_peaks(rank)
+    driver = {}
+    try:
+        driver = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
-        return None, None, None
+        pass
+    hbm_peak = float(driver.get("hbm_gbs", 6650.0))
+    n, err = ncu_pass(args, W, H, sc.render_variant())
+    wc = walker_counts(w["name"], W, H) or counters_build_counts(sb, w, W, H, cam, light)
+    rf = {"bound": "issue", "unit": "Gwarp-inst/s", "kernel": "k_render",
+          "peak": round(peaks["issue_peak_gwarpinst_s"], 1),
+          "peak_source": f"{peaks['sms']} SMs x 4 schedulers x {peaks['sm_clock_mhz_max']:.0f} MHz; an FFMA / integer-ALU interleave "
+                         f"measured {peaks['issue_gwarpinst_s']:.1f} in this run (snl_measure_peaks, builder-measured)",
+          "launch_ms": round(ms_per_launch, 4)}
+    if n:
+        inst, tinst = n["smsp__inst_executed.sum"], n.get("smsp__thread_inst_executed.sum", 0.0)
+        dram = n.get("dram__bytes_read.sum", 0.0) + n.get("dram__bytes_write.sum", 0.0)
+        lanes = tinst / inst if inst else 0.0
+        ach = inst / t / 1e9
+        sm_clk = (clocks or {}).get("sm_mhz") or peaks["sm_clock_mhz_max"]
+        wave = n.get("l1tex__data_pipe_lsu_wavefronts.sum", 0.0)
+        rf.update({
+            "achieved": round(ach, 1), "frac": round(ach / peaks["issue_peak_gwarpinst_s"], 4),
+            "warp_instructions": int(inst), "active_lanes": round(lanes, 2),
+            "useful_frac": round(ach / peaks["issue_peak_gwarpinst_s"] * lanes / 32.0, 4),
+            "traffic": int(dram), "kernel_profiled": n.get("kernel"), "registers": int(n.get("launch__registers_per_thread", 0)),
+            "l1": {"wavefronts": int(wave), "frac": round(wave / (peaks["sms"] * sm_clk * 1e6 * t), 4),
+                   "frac_is": "LSU data-pipe wavefronts / (SMs x SM clock x launch time): one wavefront per SM and cycle",
+                   "bytes": int(n.get("l1tex__t_bytes.sum", 0)), "achieved_gbs": round(n.get("l1tex__t_bytes.sum", 0) / t / 1e9, 1),
+                   "peak_gbs": round(peaks["l1_gbs"], 1), "ncu_throughput_pct": n.get("l1tex__throughput.avg.pct_of_peak_sustained_elapsed")},
+            "l2": {"bytes": int(n.get("lts__t_bytes.sum", 0)), "achieved_gbs": round(n.get("lts__t_bytes.sum", 0) / t / 1e9, 1),
+                   "peak_gbs": round(peaks["l2_gbs"], 1), "frac": round(n.get("lts__t_bytes.sum", 0) / t / 1e9 / peaks["l2_gbs"], 4),
+                   "ncu_throughput_pct": n.get("lts__throughput.avg.pct_of_peak_sustained_elapsed")},
+            "hbm": {"bytes": int(dram), "achieved_gbs": round(dram / t / 1e9, 1), "peak_gbs": hbm_peak,
+                    "dram_frac": round(dram / t / 1e9 / hbm_peak, 4),
+                    "peak_source": "MEASURED_PEAKS.json hbm_gbs (driver-measured copy)" if driver else "6650 GB/s fallback"},
+            "ncu_issue_active_pct": n.get("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+            "counts_source": "ncu pass of this bench run: same workload, camera and kept k_render variant, one launch, child process, "
+                             "after the timed region (counts and ratios only; launch_ms is the un-profiled CUDA-event time)"})
+    else:
+        rf.update({"achieved": None, "frac": None, "traffic": None, "counts_source": err})
+    if wc:
+        ab = 32 * wc["box_tests"] + 64 * wc["tri_tests"] + 16 * wc["rays"] + 64 * wc["shaded_hits"] + 3 * W * H
+        rf["algorithmic"] = {"bytes_per_launch": int(ab), "gbs": round(ab / t / 1e9, 1), "box_tests": wc["box_tests"],
+                             "tri_tests": wc["tri_tests"], "rays": wc["rays"], "source": wc.get("source"),
+                             "formula": "32 B x boxes tested (BVH::Node) + 64 B x triangles tested + 16 B hit record per ray + 64 B "
+                                        "ShTriangle per shaded hit + 3 B per pixel (SURVEY 8d)",
+                             "vs_l1_peak": round(ab / t / 1e9 / peaks["l1_gbs"], 4), "vs_hbm_peak": round(ab / t / 1e9 / hbm_peak, 4)}
+    rf["peaks_builder_measured"] = {k: round(v, 1) if isinstance(v, float) else v for k, v in peaks.items()}
+    return rf
 
 
 def run_ours(args, w, W, H):
@@ -205,27 +318,19 @@ def run_ours(args, w, W, H):
     bmin, bmax = sc.bbox()
     stream = torch.cuda.ExternalStream(sc.stream(), device=dev)
     pitch = W * 3
-    tbw, tbh = [int(x) for x in args.tile.lower().split("x")]
-    tiles = farm.tiles_for_rank(W, H, rank, world, bw=tbw, bh=tbh) if world > 1 else None
-
-    # The frame lives in rank 0's HBM. "p2p": the other ranks map it (CUDA IPC) and k_render stores into it over
-    # NVLink. "nccl": every rank renders into a local frame and the tiles are gathered with torch.distributed.
-    image = None
-    if world > 1 and args.compose == "p2p":
-        handle = [None]
-        if rank == 0:
-            frame, handle[0] = sc.frame_create(W, H)
-        dist.broadcast_object_list(handle, src=0)
-        if rank != 0:
-            frame = sc.frame_open(handle[0])
-    elif world > 1:
-        image = torch.zeros((H, W, 3), dtype=torch.uint8, device=dev)
-        frame = image.data_ptr()
-    else:
-        frame, _ = sc.frame_create(W, H)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    # N > 1: farm.Farm = bootstrap of snl_comm_* / snl_render_multi ("p2p": shared cursor, peer stores into rank 0's
+    # frame, in-stream completion, banded device->host copy) or the static tile split + NCCL gather ("nccl")
+    fm = farm.Farm(sc, dist, W, H, compose="p2p" if args.compose == "p2p" else "gather") if world > 1 else None
+    frame = sc.frame_create(W, H)[0] if world == 1 else None
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev).fill_(1)  # > 126 MB L2
+    flush64 = flush.view(torch.int64)
     host_img = torch.empty((H, W, 3), dtype=torch.uint8).pin_memory()
     host_np = host_img.numpy()
+
+    def l2_flush():
+        # READ 256 MiB: the scene leaves L2 and only clean lines stay behind (a written buffer would be evicted as
+        # dirty lines during the timed kernel and show up in its DRAM traffic)
+        return flush64.sum()
 
     def barrier():
         if world > 1:
@@ -239,36 +344,30 @@ def run_ours(args, w, W, H):
 
     def step_resident(i):
         cam = set_step(i)
-        flush.fill_(i & 255)
+        l2_flush()
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
-        sc.render_dev(cam, W, H, frame, pitch, tiles=tiles, rank=rank)
-        if image is not None:
-            with torch.cuda.stream(stream):
-                farm.gather_frame(dist, image, W, H, rank, world)
-        e1.record(stream)
-        st = sc.sync()
+        if fm is None:
+            sc.render_dev(cam, W, H, frame, pitch, rank=rank)
+            e1.record(stream)
+            st = sc.sync()
+        else:
+            _, st = fm.render(cam, host=False)  # rank 0 returns once every rank's packets are in its frame
+            e1.record(stream)
         torch.cuda.synchronize(dev)
         return e0.elapsed_time(e1), st["rays"]
 
     def step_e2e(i):
         """The host-facing call: camera in, BGR8 frame out to pinned host memory on rank 0."""
         cam = set_step(i)
-        flush.fill_(i & 255)
+        l2_flush()
         barrier()
         t0 = time.perf_counter()
-        if world == 1:
+        if fm is None:
             _, st = sc.render(cam, W, H, out=host_np)
         else:
-            sc.render_dev(cam, W, H, frame, pitch, tiles=tiles, rank=rank)
-            if image is not None:
-                with torch.cuda.stream(stream):
-                    farm.gather_frame(dist, image, W, H, rank, world)
-            st = sc.sync()
-            dist.barrier()  # every rank's tiles have landed in rank 0's frame
-            if rank == 0:
-                sc.frame_read(frame, W, H, out=host_np)
+            _, st = fm.render(cam, out=host_np)
         return (time.perf_counter() - t0) * 1e3, st["rays"]
 
     for i in range(args.warmup):
@@ -297,85 +396,69 @@ def run_ours(args, w, W, H):
 
     # back-to-back replay of the same step (no flush, no per-step sync) for ~1 s: keeps the GPU under load long
     # enough for nvidia-smi to sample clocks / throttle reasons, and gives the streaming (pipelined) frame rate
-    sus_frames, sus_rays = 0, 0
+    sus_frames, sus_rays1 = 0, 0
     cam = set_step(args.warmup)
-    st1 = None
-    sc.render_dev(cam, W, H, frame, pitch, tiles=tiles, rank=rank)
-    st1 = sc.sync()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     t0 = time.time()
-    while time.time() - t0 < args.sustain:
-        for _ in range(50):
-            sc.render_dev(cam, W, H, frame, pitch, tiles=tiles, rank=rank)
-        sus_frames += 50
-        sc.sync()
+    n_sus = max(1, int(args.sustain / max(1e-4, (sum(ms) / len(ms)) * 1e-3)))  # same frame count on every rank
+    for k in range(n_sus):
+        if fm is None:
+            sc.render_dev(cam, W, H, frame, pitch, rank=rank)
+            if k % 50 == 49 or k == n_sus - 1:
+                sus_rays1 = sc.sync()["rays"]
+        else:
+            sus_rays1 = fm.render(cam, host=False)[1]["rays"]
+        sus_frames += 1
     e1.record(stream)
     torch.cuda.synchronize(dev)
     sus_ms = e0.elapsed_time(e1)
     clocks = sampler.summary()
     clocks["window"] = "timed steps + e2e steps + %.1f s back-to-back replay of the step" % args.sustain
+    # rank 0 holds the frame's summed TreeStats (snl_render_multi sums them in-stream); the gather compose all-reduces them
     ms_t = torch.tensor(ms + e2e_ms + [sus_ms], dtype=torch.float64, device=dev)
-    rays_t = torch.tensor(rays + e2e_rays + [float(st1["rays"]) * sus_frames], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)    # a frame is done when its slowest rank is done
-        dist.all_reduce(rays_t, op=dist.ReduceOp.SUM)  # TreeStats summed over the ranks (src/server.cpp:403-418)
     K = args.steps
-    total_ms, total_rays = float(ms_t[:K].sum()), float(rays_t[:K].sum())
-    e2e_total_ms, e2e_total_rays = float(ms_t[K:2 * K].sum()), float(rays_t[K:2 * K].sum())
-    sus_value = float(rays_t[2 * K]) / (float(ms_t[2 * K]) * 1e-3) / 1e6
+    total_ms, total_rays = float(ms_t[:K].sum()), float(sum(rays))
+    e2e_total_ms, e2e_total_rays = float(ms_t[K:2 * K].sum()), float(sum(e2e_rays))
+    sus_value = float(sus_rays1) * sus_frames / (float(ms_t[2 * K]) * 1e-3) / 1e6
     if rank != 0:
+        if fm:
+            fm.close()
         sc.close()
         if dist:
             dist.destroy_process_group()
         return
     value = total_rays / (total_ms * 1e-3) / 1e6
-    compose = {1: "none (1 GPU)"}.get(world, "p2p: k_render stores tiles into rank 0's frame through CUDA-IPC peer memory (NVLink)"
-                                      if args.compose == "p2p" else "nccl gather of packed tiles to rank 0")
+    compose = {1: "none (1 GPU)"}.get(world, "p2p (snl_render_multi): every rank's persistent k_render fetches packet batches from a shared cursor "
+                                             "and stores them into rank 0's frame through CUDA-IPC peer memory (NVLink), in-stream completion"
+                                      if args.compose == "p2p" else "static 16x64 tile split + NCCL gather of packed tiles to rank 0")
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K,
         "warmup": args.warmup, "ms_per_step": round(total_ms / K, 4), "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "scene assets under assets/ (reference scenes; sponza_like is procedurally generated), synthetic camera path",
         "config": {"workload": f"{w['name']} {W}x{H}: {w['desc']}", "rays_per_step": round(total_rays / K),
-                   "l2": "256 MiB buffer written between timed steps (L2 flush)",
+                   "l2": "256 MiB buffer READ between timed steps (L2 flush that leaves no dirty lines)",
                    "timing": "CUDA events on the scene stream around each step (barrier + sync on both sides), "
                              "per-step max over ranks, summed",
-                   "compose": compose, "tiles": f"{args.tile}, shuffled per group of N ranks" if world > 1 else "full frame"},
+                   "compose": compose},
         "gpu_launches": int(launches), "clocks": clocks, "wall_s": round(wall, 3),
         "sustained": {"value": round(sus_value, 2), "unit": UNIT, "frames": sus_frames,
-                      "note": "same step replayed back to back, no L2 flush, no per-step sync, camera fixed"},
+                      "note": "same step replayed back to back, no L2 flush, camera fixed"},
     }
     ev = e2e_total_rays / (e2e_total_ms * 1e-3) / 1e6
     line["e2e"] = {"value": round(ev, 2), "unit": UNIT, "h2d_bytes_per_step": (52 + 36 * (1 if w["lit"] else 0)) * world,
-                   "d2h_bytes_per_step": W * H * 3 + 72 * world, "ms_per_step": round(e2e_total_ms / K, 4),
+                   "d2h_bytes_per_step": W * H * 3 + 72, "ms_per_step": round(e2e_total_ms / K, 4),
                    "timing": "host wall clock around the host-facing render call (camera + light in, BGR8 frame out to "
-                             "pinned host memory on rank 0" + (", incl. the cross-rank barrier)" if world > 1 else ")")}
-    # roofline of the dominant kernel (k_render): algorithmic bytes / measured launch time
-    cam, light = camera_for_step(sb, bmin, bmax, w["inside"], args.warmup)
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    peak = float(peaks.get("hbm_gbs", 6650.0))
+                             "pinned host memory on rank 0" + ("; max over ranks of snl_render_multi, no host collective inside)" if world > 1 else ")")}
     if world == 1 and not args.no_extras:
-        abytes, cst = algorithmic_bytes(sb, w, W, H, cam, light)
-        if abytes:
-            ach = abytes / (total_ms / K * 1e-3) / 1e9
-            traffic, tsrc, ncu_sm = load_traffic(w["name"], W, H)
-            line["roofline"] = {"bound": "hbm", "achieved": round(ach, 1), "peak": peak, "unit": "GB/s",
-                                "frac": round(ach / peak, 4), "traffic": traffic, "traffic_source": tsrc,
-                                "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "6650 GB/s (of fallback)",
-                                "note": "algorithmic bytes (64 B/node visit, 48|64 B/triangle test, 16 B/ray, 64 B/shaded hit, "
-                                        "3 B/pixel) are served by L1/L2 - the scene is L2-resident, DRAM traffic is ~0 - so "
-                                        "frac vs the HBM copy peak can exceed 1; the binding resource is SM issue slots "
-                                        "(see DESIGN.md, profiles/)",
-                                "algorithmic_bytes_per_launch": int(abytes),
-                                "node_visits": cst["node_visits"], "tri_tests": cst["tri_tests"] + cst["gtri_tests"]}
-            if ncu_sm:  # what actually binds the kernel, from the committed ncu capture (not measured in this run)
-                line["roofline"]["sm_limiters_from_ncu"] = ncu_sm
+        try:
+            line["roofline"] = build_roofline(sb, args, w, W, H, sc, total_ms / K, clocks, local_rank)
+        except Exception as e:  # noqa: BLE001
+            line["roofline"] = {"bound": "issue", "achieved": None, "frac": None, "traffic": None, "error": str(e)[:300]}
     if world == 1 and not args.no_cpu_baseline:
         threads = host_threads()
         reference_frames(w, W, H, 1, threads)
@@ -387,6 +470,8 @@ def run_ours(args, w, W, H):
                                 "sample": f"{frames} full {W}x{H} frames of the same workload through the reference's "
                                           f"Render() (oracle/_ref, veclib {variant}), {threads} threads"}
     print(json.dumps(line), file=JSON_OUT, flush=True)
+    if fm:
+        fm.close()
     sc.close()
     if dist:
         dist.destroy_process_group()
@@ -406,7 +491,9 @@ def main():
     from snail_b200 import workloads
     w = workloads.resolve(args.workload)
     W, H = [int(x) for x in args.res.lower().split("x")]
-    if args.impl == "reference":
+    if args.ncu_child:
+        ncu_child(args, w, W, H)
+    elif args.impl == "reference":
         run_reference(args, w, W, H)
     else:
         run_ours(args, w, W, H)

@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define SNL_ABI_VERSION 2
+#define SNL_ABI_VERSION 3
 
 typedef enum snl_status {
 	SNL_OK = 0,
@@ -244,6 +244,32 @@ int snl_frame_open(snl_scene *, const unsigned char ipc_handle[SNL_IPC_HANDLE_BY
 int snl_frame_close(snl_scene *, void *bgr8_dev); /* frees (owner) or unmaps (peer) */
 int snl_frame_read(snl_scene *, const void *bgr8_dev, int W, int H, unsigned char *bgr8_host, size_t host_pitch);
 
+/* Render() over the GPUs of one box behind this ABI: replaces the reference's farm loop (src/server.cpp:227-265 tile
+ * split, :330-418 receive loop + stats merge; src/node.cpp:308-346 node side; src/comm_mpi.cpp transport). Every GPU
+ * holds a replica of the scene (one snl_scene each, same geometry / materials / lights / options); the frame lives in
+ * rank 0's HBM in a segment the other ranks map. Per frame all ranks run ONE persistent k_render each that fetches
+ * packet batches from a shared cursor (system-scope atomics over NVLink: the GPUs balance themselves, where the
+ * reference dealt tiles statically), stores its packets straight into rank 0's frame and counts them off per row band;
+ * rank 0 copies band i to the host while band i+1 is still rendering, and sums the TreeStats. No host-side collective
+ * per frame; every device-side wait has a time-out (SNL_ERR_STATE) instead of a hang.
+ *   between processes (one rank per process, e.g. under torchrun / mpirun):
+ *       rank 0:  snl_comm_create_root(scene, world, W, H, blob, &comm);  send blob to the others with ANY byte transport
+ *       rank r:  snl_comm_attach(scene, r, blob, &comm);
+ *   inside one process driving n devices:  snl_comm_create_local(scenes, n, W, H, &comm)   (scenes[0] = rank 0)
+ * snl_render_multi is collective: every rank calls it once per frame with the same camera. bgr8_host (rank 0 only,
+ * may be NULL to keep the frame on the device, see snl_comm_frame) receives the frame as snl_render writes it. stats:
+ * rank 0 gets the sum over the ranks, another process its own share. gVals[9] is not available here. */
+typedef struct snl_comm snl_comm;
+#define SNL_COMM_BLOB_BYTES 96
+int snl_comm_create_root(snl_scene *, int world, int W, int H, unsigned char blob[SNL_COMM_BLOB_BYTES], snl_comm **out);
+int snl_comm_attach(snl_scene *, int rank, const unsigned char blob[SNL_COMM_BLOB_BYTES], snl_comm **out);
+int snl_comm_create_local(snl_scene *const *scenes, int n, int W, int H, snl_comm **out);
+int snl_comm_info(const snl_comm *, int *world, int *W, int *H, int *localRanks);
+int snl_render_multi(snl_comm *, const snl_camera *cam, unsigned char *bgr8_host, size_t pitch, snl_stats *stats);
+/* device pointer (rank 0's address space) + pitch of the frame the last snl_render_multi produced */
+int snl_comm_frame(snl_comm *, void **bgr8_dev, size_t *pitch);
+void snl_comm_destroy(snl_comm *);
+
 /* Builder-side ceilings for the roofline of the traversal kernels (bench.py `roofline`): the reference's scenes are
  * L2-resident on a B200 and the walk is served by L1, so what bounds k_render is instruction issue and L1 / L2
  * bandwidth, not HBM. Streaming microbenchmarks timed with CUDA events on `device` (snail_b200/csrc/snl_peaks.cu);
@@ -262,6 +288,11 @@ int snl_measure_peaks(int device, snl_peaks *out);
 
 /* Number of kernels this library launched on the scene since creation (bench.py's gpu_launches). */
 uint64_t snl_scene_launch_count(snl_scene *);
+
+/* Which register budget of k_render the scene settled on for its current workload (0: 64 registers / 4 CTAs per SM,
+ * 1: 48 registers / 5 CTAs per SM; -1: not decided yet - the first full frame of a workload is rendered three times with
+ * each and the faster is kept; SNL_RENDER_VARIANT=0|1 pins it). */
+int snl_scene_render_variant(snl_scene *);
 
 /* cudaStream_t of the scene, as an integer, so a caller can order its own work / CUDA events after ours. */
 uint64_t snl_scene_stream(snl_scene *);

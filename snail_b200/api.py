@@ -20,11 +20,12 @@ ABI_SYMBOLS = [
     "snl_scene_set_geometry", "snl_scene_set_materials", "snl_scene_set_lights", "snl_set_options",
     "snl_scene_load_obj", "snl_scene_counts", "snl_scene_copy_host_bvh", "snl_scene_bbox", "snl_trace_primary",
     "snl_trace_rays", "snl_trace_shadow", "snl_raytrace", "snl_render", "snl_render_dev", "snl_render_farm", "snl_scene_sync",
-    "snl_scene_launch_count", "snl_scene_stream", "snl_host_scene_load_obj", "snl_host_scene_free",
+    "snl_scene_launch_count", "snl_scene_render_variant", "snl_scene_stream", "snl_host_scene_load_obj", "snl_host_scene_free",
     "snl_host_scene_counts", "snl_host_scene_copy", "snl_host_scene_material", "snl_host_scene_texture",
     "snl_scene_set_host_scene", "snl_scene_build_device", "snl_scene_build_ms", "snl_scene_set_instances",
     "snl_trace_primary_inst", "snl_scene_copy_dbvh", "snl_host_dbvh_build", "snl_frame_create", "snl_frame_open", "snl_frame_close", "snl_frame_read",
-    "snl_measure_peaks",
+    "snl_measure_peaks", "snl_comm_create_root", "snl_comm_attach", "snl_comm_create_local", "snl_comm_info", "snl_render_multi",
+    "snl_comm_frame", "snl_comm_destroy",
 ]
 
 # reference record layouts (src/bvh/tree.h:60-72, src/triangle.h:133-135,181-230)
@@ -143,6 +144,7 @@ def load_library(counters: bool = False) -> C.CDLL:
     L.snl_scene_sync.argtypes = [vp, C.POINTER(Stats)]
     L.snl_scene_launch_count.restype = C.c_uint64
     L.snl_scene_launch_count.argtypes = [vp]
+    L.snl_scene_render_variant.argtypes = [vp]
     L.snl_scene_stream.restype = C.c_uint64
     L.snl_scene_stream.argtypes = [vp]
     L.snl_host_scene_load_obj.restype = vp
@@ -159,6 +161,14 @@ def load_library(counters: bool = False) -> C.CDLL:
     L.snl_frame_close.argtypes = [vp, vp]
     L.snl_frame_read.argtypes = [vp, vp, i, i, vp, C.c_size_t]
     L.snl_measure_peaks.argtypes = [i, C.POINTER(Peaks)]
+    L.snl_comm_create_root.argtypes = [vp, i, i, i, C.c_char_p, C.POINTER(vp)]
+    L.snl_comm_attach.argtypes = [vp, i, C.c_char_p, C.POINTER(vp)]
+    L.snl_comm_create_local.argtypes = [C.POINTER(vp), i, i, i, C.POINTER(vp)]
+    L.snl_comm_info.argtypes = [vp, ip, ip, ip, ip]
+    L.snl_render_multi.argtypes = [vp, C.POINTER(Camera), vp, C.c_size_t, C.POINTER(Stats)]
+    L.snl_comm_frame.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]
+    L.snl_comm_destroy.argtypes = [vp]
+    L.snl_comm_destroy.restype = None
     _libs[path] = L
     return L
 
@@ -478,8 +488,78 @@ class Scene:
     def launch_count(self):
         return int(self.L.snl_scene_launch_count(self.h))
 
+    def render_variant(self):
+        return int(self.L.snl_scene_render_variant(self.h))
+
     def stream(self):
         return int(self.L.snl_scene_stream(self.h))
+
+
+COMM_BLOB_BYTES = 96
+
+
+class Comm:
+    """Render() over the GPUs of one box (snl_comm_* / snl_render_multi, include/snail_b200.h): the frame lives on rank
+    0, every rank's persistent k_render pulls packet batches from a shared cursor and stores into it over NVLink.
+
+      Comm.root(scene, world, W, H) -> (comm, blob)    rank 0; send `blob` (96 bytes) to the others by any transport
+      Comm.attach(scene, rank, blob)                   ranks 1..world-1 (other processes)
+      Comm.local([scene0, scene1, ...], W, H)          one process driving several devices
+    render(cam, out) is collective: every rank calls it once per frame with the same camera."""
+
+    def __init__(self, L, handle, scenes, rank):
+        self.L, self.h, self.scenes, self.rank = L, handle, scenes, rank
+        v = [C.c_int() for _ in range(4)]
+        L.snl_comm_info(handle, *[C.byref(x) for x in v])
+        self.world, self.W, self.H, self.local_ranks = [x.value for x in v]
+
+    @staticmethod
+    def _check(L, code):
+        if code != 0:
+            raise SnlError(code, L.snl_last_error().decode())
+
+    @classmethod
+    def root(cls, scene, world, W, H):
+        blob = C.create_string_buffer(COMM_BLOB_BYTES)
+        h = C.c_void_p()
+        cls._check(scene.L, scene.L.snl_comm_create_root(scene.h, world, W, H, blob, C.byref(h)))
+        return cls(scene.L, h, [scene], 0), blob.raw
+
+    @classmethod
+    def attach(cls, scene, rank, blob: bytes):
+        h = C.c_void_p()
+        cls._check(scene.L, scene.L.snl_comm_attach(scene.h, rank, blob, C.byref(h)))
+        return cls(scene.L, h, [scene], rank)
+
+    @classmethod
+    def local(cls, scenes, W, H):
+        arr = (C.c_void_p * len(scenes))(*[s.h for s in scenes])
+        h = C.c_void_p()
+        cls._check(scenes[0].L, scenes[0].L.snl_comm_create_local(arr, len(scenes), W, H, C.byref(h)))
+        return cls(scenes[0].L, h, list(scenes), 0)
+
+    def render(self, cam: Camera, out=None, host=True):
+        """Returns (frame or None, stats). Rank 0: the (H, W, 3) frame in `out` (host=False: the frame stays on the
+        device, see frame()) and TreeStats summed over the ranks; other ranks: (None, their own share)."""
+        st = Stats()
+        ptr, pitch = None, 0
+        if self.rank == 0 and host:
+            if out is None:
+                out = np.zeros((self.H, self.W, 3), np.uint8)
+            ptr, pitch = _ptr(out), out.strides[0]
+        self._check(self.L, self.L.snl_render_multi(self.h, C.byref(cam), ptr, pitch, C.byref(st)))
+        return (out if self.rank == 0 and host else None), st.as_dict()
+
+    def frame(self):
+        """(device pointer, pitch) of the frame the last render() produced (rank 0's address space)."""
+        p, pitch = C.c_void_p(), C.c_size_t()
+        self._check(self.L, self.L.snl_comm_frame(self.h, C.byref(p), C.byref(pitch)))
+        return p.value, pitch.value
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.snl_comm_destroy(self.h)
+            self.h = None
 
 
 def bench_camera(bmin, bmax, inside=False):

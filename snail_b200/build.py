@@ -14,7 +14,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libsnail_b200.so")
 LIB_COUNTERS = os.path.join(HERE, "libsnail_b200_counters.so")
 
-SOURCES = ["snl_kernels.cu", "snl_wavefront.cu", "snl_build.cu", "snl_capi.cu", "snl_peaks.cu", "snl_host_scene.cpp", "snl_host_dbvh.cpp"]
+SOURCES = ["snl_kernels.cu", "snl_wavefront.cu", "snl_build.cu", "snl_capi.cu", "snl_comm.cu", "snl_peaks.cu", "snl_host_scene.cpp", "snl_host_dbvh.cpp"]
 HEADERS = ["snl_device.cuh", "snl_kernels.h", "snl_scene.h", "snl_scene_dev.h", "snl_types.h", "snl_host_scene.h",
            os.path.join("..", "..", "include", "snail_b200.h")]
 
@@ -54,13 +54,40 @@ def build_library(force: bool = False, counters: bool = False, verbose: bool = F
     flags += list(extra)
     if verbose:
         flags += ["-Xptxas", "-v"]
-    cmd = [_nvcc(), "-shared", *flags, "-I", os.path.join(HERE, "..", "include"),
-           *[os.path.join(CSRC, s) for s in SOURCES], "-o", target + ".tmp", "-lz"]
+    # one nvcc per translation unit, in parallel; objects are cached by (flags, source + header contents)
+    import hashlib
+    from concurrent.futures import ThreadPoolExecutor
+    inc = ["-I", os.path.join(HERE, "..", "include")]
+    hdr_digest = hashlib.sha256(b"".join(open(os.path.join(CSRC, h), "rb").read() for h in HEADERS)).hexdigest()
+    objdir = os.path.join(HERE, "build")
+    os.makedirs(objdir, exist_ok=True)
+
+    def compile_one(src):
+        key = hashlib.sha256((" ".join(flags) + hdr_digest).encode() + open(os.path.join(CSRC, src), "rb").read()).hexdigest()[:20]
+        obj = os.path.join(objdir, f"{os.path.splitext(src)[0]}.{key}.o")
+        if os.path.exists(obj) and not verbose:
+            return obj, ""
+        cmd = [_nvcc(), "-c", *flags, *inc, os.path.join(CSRC, src), "-o", obj + ".tmp"]
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + res.stdout + res.stderr)
+        os.replace(obj + ".tmp", obj)
+        return obj, res.stderr
+
+    with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
+        results = list(ex.map(compile_one, SOURCES))
+    if verbose:
+        print("".join(r[1] for r in results))
+    keep = {os.path.basename(r[0]) for r in results}
+    for f in os.listdir(objdir):  # drop objects of older source versions of the same configuration
+        stem = f.split(".")[0]
+        if f.endswith(".o") and f not in keep and any(stem == os.path.splitext(x)[0] for x in SOURCES) and \
+                os.path.getmtime(os.path.join(objdir, f)) < __import__("time").time() - 6 * 3600:
+            os.remove(os.path.join(objdir, f))
+    cmd = [_nvcc(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a", *[r[0] for r in results], "-o", target + ".tmp", "-lz"]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + res.stdout + res.stderr)
-    if verbose:
-        print(res.stderr)
+        raise RuntimeError("nvcc link failed:\n" + " ".join(cmd) + "\n" + res.stdout + res.stderr)
     os.replace(target + ".tmp", target)
     return target
 

@@ -174,6 +174,14 @@ int sync_and_stats(snl_scene *s, snl_stats *stats) {
 	return SNL_OK;
 }
 
+}  // namespace
+namespace snl {
+int ensure_pre(snl_scene *s, PreCacheEntry &e, const float origin[3]);
+int make_scene_dev(snl_scene *s, SceneDev &S, const float *shareOrigin, unsigned *shared);
+void make_raygen(const snl_camera &c, int W, int H, RayGenParams &g);
+}
+namespace {
+
 int begin_call(snl_scene *s) {
 	SNL_REQUIRE(s, SNL_ERR_INVALID, "null scene");
 	SNL_CUDA(cudaSetDevice(s->device));
@@ -189,8 +197,10 @@ int end_call(snl_scene *s) {
 	return SNL_OK;
 }
 
+}  // namespace
+
 // Per-origin triangle records, recomputed only when the origin changes.
-int ensure_pre(snl_scene *s, PreCacheEntry &e, const float origin[3]) {
+int snl::ensure_pre(snl_scene *s, PreCacheEntry &e, const float origin[3]) {
 	if(e.valid && memcmp(e.origin, origin, 12) == 0)
 		return SNL_OK;
 	SNL_CUDA(e.buf.reserve((size_t)s->nTris));
@@ -207,7 +217,7 @@ int ensure_pre(snl_scene *s, PreCacheEntry &e, const float origin[3]) {
 // placing a light, src/rtracer.cpp:270-281 - shares the camera's per-origin triangle records instead of getting a
 // second identical copy (half the PreTri bytes competing for L1 / L2, one k_pretransform less per frame). The caller
 // fills S.lightPre[i] for the lights flagged in *shared once the camera's records are up to date.
-int make_scene_dev(snl_scene *s, SceneDev &S, const float *shareOrigin = nullptr, unsigned *shared = nullptr) {
+int snl::make_scene_dev(snl_scene *s, SceneDev &S, const float *shareOrigin, unsigned *shared) {
 	memset(&S, 0, sizeof(S));
 	S.nodes = s->dNodes.ptr;
 	S.gtris = s->dTris.ptr;
@@ -277,7 +287,7 @@ int make_scene_dev(snl_scene *s, SceneDev &S, const float *shareOrigin = nullptr
 }
 
 // RayGenerator::RayGenerator (src/ray_generator.cpp:4-14), same operation order.
-void make_raygen(const snl_camera &c, int W, int H, RayGenParams &g) {
+void snl::make_raygen(const snl_camera &c, int W, int H, RayGenParams &g) {
 	float invW = 1.0f / float(W), invH = 1.0f / float(H);
 	invW *= float(W) / float(H);
 	const float addx[4] = {0.0f, 1.0f, 0.0f, 1.0f}, addy[4] = {0.0f, 0.0f, 1.0f, 1.0f};
@@ -295,7 +305,31 @@ void make_raygen(const snl_camera &c, int W, int H, RayGenParams &g) {
 	}
 }
 
-}  // namespace
+static const float kRankTint[16][3] = {  // src/render.cpp:119-128
+	{0.6f, 0.6f, 0.6f}, {0.6f, 0.6f, 1.0f}, {0.6f, 1.0f, 0.6f}, {0.6f, 1.0f, 1.0f}, {1.0f, 0.6f, 0.6f}, {1.0f, 0.6f, 1.0f},
+	{1.0f, 1.0f, 0.6f}, {1.0f, 1.0f, 1.0f}, {0.3f, 0.3f, 0.3f}, {0.3f, 0.3f, 1.0f}, {0.3f, 0.7f, 0.3f}, {0.3f, 0.7f, 0.7f},
+	{0.7f, 0.3f, 0.3f}, {0.7f, 0.3f, 0.7f}, {0.7f, 0.7f, 0.3f}, {0.7f, 1.7f, 0.7f}};
+
+// What one Render() call needs on the device before its k_render: the scene argument (lights, options, per-origin
+// triangle records of the camera and the lights, shared where a light sits at the camera) and the ray generator.
+int snl::prepare_frame(snl_scene *s, const snl_camera *cam, int W, int H, int rank, SceneDev &S, RayGenParams &g) {
+	unsigned sharedLights = 0;
+	if(int r = make_scene_dev(s, S, cam->pos, &sharedLights))
+		return r;
+	SNL_REQUIRE(!(S.instances && S.gvSuper), SNL_ERR_UNSUPPORTED, "gVals[9] supersampling is not available on an instanced scene");
+	if(s->gVals[8]) {
+		S.gvTint = 1;
+		memcpy(S.tint, kRankTint[(unsigned)rank % 16], 12);
+	}
+	if(int r = ensure_pre(s, s->originPre, cam->pos))
+		return r;
+	for(int i = 0; i < S.nLights; i++)
+		if(sharedLights >> i & 1)
+			S.lightPre[i] = s->originPre.set();
+	const int scale = s->gVals[9] ? 2 : 1;  // src/render.cpp:60-62
+	make_raygen(*cam, W * scale, H * scale, g);
+	return SNL_OK;
+}
 
 // =================================================================================================================
 extern "C" {
@@ -785,6 +819,7 @@ int snl_scene_bbox(snl_scene *s, float bmin[3], float bmax[3]) {
 }
 
 uint64_t snl_scene_launch_count(snl_scene *s) { return s ? s->launches : 0; }
+int snl_scene_render_variant(snl_scene *s) { return s ? s->tune.choice : -1; }
 uint64_t snl_scene_stream(snl_scene *s) { return s ? (uint64_t)(uintptr_t)s->stream : 0; }
 
 // ---- compute entry points ---------------------------------------------------------------------------------------
@@ -825,7 +860,7 @@ static int trace_primary_impl(snl_scene *s, const snl_camera *cam, int W, int H,
 	SNL_TRY(scratch(s, 1, n, &dT));
 	SNL_TRY(scratch(s, 2, n * 2, &dB));
 	SceneDev S;
-	SNL_TRY(make_scene_dev(s, S));
+	SNL_TRY(make_scene_dev(s, S, nullptr, nullptr));
 	SNL_TRY(ensure_pre(s, s->originPre, cam->pos));
 	RayGenParams g;
 	make_raygen(*cam, W, H, g);
@@ -878,7 +913,7 @@ int snl_trace_rays(snl_scene *s, const float *o3, const float *d3, const unsigne
 	int *dId = (int *)res;
 	float *dT = (float *)(res + (size_t)n * 4), *dB = (float *)(res + (size_t)n * 8);
 	SceneDev S;
-	SNL_TRY(make_scene_dev(s, S));
+	SNL_TRY(make_scene_dev(s, S, nullptr, nullptr));
 	if(sharedOrigin)
 		SNL_TRY(ensure_pre(s, s->originPre, o3));
 	SNL_CUDA(launch_trace_rays(S, s->originPre.set(), dO, dD, dM, n, sharedOrigin != 0, dId, dT, dB, s->stream));
@@ -905,7 +940,7 @@ int snl_trace_shadow(snl_scene *s, const float origin[3], const float *d3, float
 	SNL_CUDA(cudaMemcpyAsync(dD, d3, (size_t)n * 12, cudaMemcpyHostToDevice, s->stream));
 	SNL_CUDA(cudaMemcpyAsync(dT, tmax_inout, (size_t)n * 4, cudaMemcpyHostToDevice, s->stream));
 	SceneDev S;
-	SNL_TRY(make_scene_dev(s, S));
+	SNL_TRY(make_scene_dev(s, S, nullptr, nullptr));
 	SNL_TRY(ensure_pre(s, s->originPre, origin));
 	SNL_CUDA(launch_trace_shadow(S, s->originPre.set(), origin, dD, dT, n, s->stream));
 	s->launches++;
@@ -926,7 +961,7 @@ int snl_raytrace(snl_scene *s, const float *o3, const float *d3, const unsigned 
 	SNL_TRY(upload_rays(s, o3, d3, mask, n, sharedOrigin, &dO, &dD, &dM));
 	SNL_TRY(scratch(s, 3, (size_t)n * 3, &dC));
 	SceneDev S;
-	SNL_TRY(make_scene_dev(s, S));
+	SNL_TRY(make_scene_dev(s, S, nullptr, nullptr));
 	if(sharedOrigin)
 		SNL_TRY(ensure_pre(s, s->originPre, o3));
 	SNL_CUDA(launch_raytrace(S, s->originPre.set(), dO, dD, dM, n, sharedOrigin != 0, dC, s->stream));
@@ -935,6 +970,9 @@ int snl_raytrace(snl_scene *s, const float *o3, const float *d3, const unsigned 
 	SNL_CUDA(cudaMemcpyAsync(rgb3, dC, (size_t)n * 12, cudaMemcpyDeviceToHost, s->stream));
 	return sync_and_stats(s, stats);
 }
+
+static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, const int *tiles, int nTiles, unsigned char *dOut,
+						 size_t pitch, int rank, unsigned char *hostOut = nullptr, size_t hostPitch = 0, bool *hostDone = nullptr);
 
 // Tile list -> packet list (RenderTask::Work's x/y loops, src/render.cpp:67-68), cached between calls.
 static int ensure_packets(snl_scene *s, const int *tiles, int nTiles, int W, int H) {
@@ -963,30 +1001,13 @@ static int ensure_packets(snl_scene *s, const int *tiles, int nTiles, int W, int
 	return SNL_OK;
 }
 
-static const float kRankTint[16][3] = {  // src/render.cpp:119-128
-	{0.6f, 0.6f, 0.6f}, {0.6f, 0.6f, 1.0f}, {0.6f, 1.0f, 0.6f}, {0.6f, 1.0f, 1.0f}, {1.0f, 0.6f, 0.6f}, {1.0f, 0.6f, 1.0f},
-	{1.0f, 1.0f, 0.6f}, {1.0f, 1.0f, 1.0f}, {0.3f, 0.3f, 0.3f}, {0.3f, 0.3f, 1.0f}, {0.3f, 0.7f, 0.3f}, {0.3f, 0.7f, 0.7f},
-	{0.7f, 0.3f, 0.3f}, {0.7f, 0.3f, 0.7f}, {0.7f, 0.7f, 0.3f}, {0.7f, 1.7f, 0.7f}};
-
 // hostOut != null (snl_render): a large full frame is rendered in row bands, each on its own stream and followed by the
 // device->host copy of its rows; *hostDone tells the caller the copies are already queued (and joined into s->stream).
 static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, const int *tiles, int nTiles, unsigned char *dOut,
-						 size_t pitch, int rank, unsigned char *hostOut = nullptr, size_t hostPitch = 0, bool *hostDone = nullptr) {
+						 size_t pitch, int rank, unsigned char *hostOut, size_t hostPitch, bool *hostDone) {
 	SceneDev S;
-	unsigned sharedLights = 0;
-	SNL_TRY(make_scene_dev(s, S, cam->pos, &sharedLights));
-	SNL_REQUIRE(!(S.instances && S.gvSuper), SNL_ERR_UNSUPPORTED, "gVals[9] supersampling is not available on an instanced scene");
-	if(s->gVals[8]) {
-		S.gvTint = 1;
-		memcpy(S.tint, kRankTint[(unsigned)rank % 16], 12);
-	}
-	SNL_TRY(ensure_pre(s, s->originPre, cam->pos));
-	for(int i = 0; i < S.nLights; i++)
-		if(sharedLights >> i & 1)
-			S.lightPre[i] = s->originPre.set();
 	RayGenParams g;
-	const int scale = s->gVals[9] ? 2 : 1;  // src/render.cpp:60-62
-	make_raygen(*cam, W * scale, H * scale, g);
+	SNL_TRY(prepare_frame(s, cam, W, H, rank, S, g));
 	const int4 *packets = nullptr;
 	if(tiles) {
 		SNL_TRY(ensure_packets(s, tiles, nTiles, W, H));
@@ -1345,3 +1366,8 @@ int snl_scene_load_obj(snl_scene *s, const char *objPath, const char *mtlPath, c
 }
 
 }  // extern "C"
+
+int snl::render_local(snl_scene *s, const snl_camera *cam, int W, int H, const int *tiles, int nTiles, unsigned char *dOut,
+					   size_t pitch, int rank) {
+	return ::render_common(s, cam, W, H, tiles, nTiles, dOut, pitch, rank, nullptr, 0, nullptr);
+}

@@ -1,0 +1,428 @@
+// snail_b200 — Render() over the GPUs of one box behind the C ABI (snl_comm_*, snl_render_multi): the replacement of the
+// reference's render farm loop (src/server.cpp:227-265 tile split, :330-418 per-frame receive loop and stats merge;
+// src/node.cpp:308-346 the node side; src/comm_mpi.cpp transport).
+//
+// The scene is replicated (one snl_scene per GPU); the frame lives in rank 0's HBM inside ONE shared segment that the
+// other ranks map (CUDA IPC between processes, peer access inside one process):
+//
+//     [ CommCtl (4 KB) | frame slot 0 | frame slot 1 ]
+//
+// Per frame `seq` (slot = seq & 1), everything in-stream, no host-side collective:
+//   rank 0   k_frame_open    waits until every rank has left frame seq-2, zeroes the slot's cursor / counters, opens it
+//   all      k_render        persistent CTAs; each fetches the next packet batch from the SHARED cursor with a
+//                            system-scope atomic (the reference's taskMap dealt tiles statically, src/server.cpp:238-248;
+//                            here the GPUs balance themselves), stores the packet into rank 0's frame over NVLink as
+//                            16-byte vectors and bumps the packet's band counter
+//   all      k_frame_publish adds the rank's TreeStats counters to the frame's (src/server.cpp:403-418), marks the rank done
+//   rank 0   k_wait_counter + cudaMemcpy2DAsync per row band on copy streams: band i goes to the host while band i+1
+//            is still being rendered; then the summed stats.
+// Every wait has a time-out that raises CommCtl::error instead of hanging the device.
+#include <cstring>
+
+#include "snl_scene.h"
+
+using namespace snl;
+
+#define SNL_CUDA(call)                                                                              \
+	do {                                                                                            \
+		cudaError_t e_ = (call);                                                                    \
+		if(e_ != cudaSuccess) {                                                                     \
+			set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+			return SNL_ERR_CUDA;                                                                    \
+		}                                                                                           \
+	} while(0)
+#define SNL_REQUIRE(cond, code, ...) \
+	do {                             \
+		if(!(cond)) {                \
+			set_error(__VA_ARGS__);  \
+			return code;             \
+		}                            \
+	} while(0)
+#define SNL_TRY(expr)    \
+	do {                 \
+		int r_ = (expr); \
+		if(r_)           \
+			return r_;   \
+	} while(0)
+
+namespace {
+
+struct CommRank {  // one rank driven by this process
+	snl_scene *scene = nullptr;
+	int rank = 0;
+	unsigned char *seg = nullptr;  // rank 0's segment as this rank's device sees it
+	bool ipc = false;              // mapped with cudaIpcOpenMemHandle (else: owned, or a peer pointer of this process)
+	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+struct Blob {  // what travels from rank 0 to the other processes (any byte transport)
+	unsigned char handle[64];
+	int world, W, H, magic;
+};
+static_assert(sizeof(Blob) <= SNL_COMM_BLOB_BYTES, "blob size");
+enum { kBlobMagic = 0x534e4c43 };
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+struct snl_comm {
+	int world = 0, W = 0, H = 0;
+	size_t pitch = 0, frameBytes = 0, segBytes = 0;
+	unsigned seq = 0;
+	std::vector<CommRank> ranks;  // 1 entry between processes, `world` entries inside one process
+	bool ownsSegment = false;
+	// rank 0's side
+	int nBands = 1, rowsPerBand = 1;
+	cudaStream_t copyStream[kCommBands] = {};
+	cudaEvent_t copyEv[kCommBands] = {}, openEv = nullptr;
+	unsigned long long *hStats = nullptr;  // pinned: 8 counters + error word
+	float lastMs = 0.0f;
+};
+
+namespace {
+
+int comm_geometry(snl_comm *c, int world, int W, int H) {
+	SNL_REQUIRE(world >= 1 && world <= kCommRanks, SNL_ERR_INVALID, "world size %d (1..%d)", world, (int)kCommRanks);
+	SNL_REQUIRE(W > 0 && H > 0, SNL_ERR_INVALID, "bad frame size %dx%d", W, H);
+	c->world = world;
+	c->W = W;
+	c->H = H;
+	c->pitch = align_up((size_t)W * 3, 16);
+	c->frameBytes = align_up(c->pitch * H, 256);
+	c->segBytes = kCommCtlBytes + 2 * c->frameBytes;
+	const int py = (H + 15) / 16;
+	c->nBands = std::min<int>(kCommBands, py);
+	c->rowsPerBand = (py + c->nBands - 1) / c->nBands;
+	c->nBands = (py + c->rowsPerBand - 1) / c->rowsPerBand;
+	return SNL_OK;
+}
+
+int comm_root_resources(snl_comm *c) {
+	CommRank &r0 = c->ranks[0];
+	SNL_CUDA(cudaSetDevice(r0.scene->device));
+	SNL_CUDA(cudaEventCreateWithFlags(&c->openEv, cudaEventDisableTiming));
+	for(int b = 0; b < c->nBands; b++) {
+		SNL_CUDA(cudaStreamCreateWithFlags(&c->copyStream[b], cudaStreamNonBlocking));
+		SNL_CUDA(cudaEventCreateWithFlags(&c->copyEv[b], cudaEventDisableTiming));
+	}
+	SNL_CUDA(cudaMallocHost(&c->hStats, 16 * sizeof(unsigned long long)));
+	return SNL_OK;
+}
+
+int comm_rank_events(CommRank &r) {
+	SNL_CUDA(cudaSetDevice(r.scene->device));
+	SNL_CUDA(cudaEventCreate(&r.ev0));
+	SNL_CUDA(cudaEventCreate(&r.ev1));
+	return SNL_OK;
+}
+
+int alloc_segment(snl_comm *c, snl_scene *s, unsigned char **seg) {
+	SNL_CUDA(cudaSetDevice(s->device));
+	void *p = nullptr;
+	SNL_CUDA(cudaMalloc(&p, c->segBytes));
+	SNL_CUDA(cudaMemset(p, 0, c->segBytes));
+	SNL_CUDA(cudaDeviceSynchronize());
+	*seg = (unsigned char *)p;
+	c->ownsSegment = true;
+	return SNL_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int snl_comm_create_root(snl_scene *s, int world, int W, int H, unsigned char blob[SNL_COMM_BLOB_BYTES], snl_comm **out) {
+	SNL_REQUIRE(s && out, SNL_ERR_INVALID, "null argument");
+	snl_comm *c = new snl_comm;
+	int r = comm_geometry(c, world, W, H);
+	CommRank r0;
+	r0.scene = s;
+	r0.rank = 0;
+	if(!r)
+		r = alloc_segment(c, s, &r0.seg);
+	c->ranks.push_back(r0);
+	if(!r)
+		r = comm_rank_events(c->ranks[0]);
+	if(!r)
+		r = comm_root_resources(c);
+	if(!r && blob) {
+		Blob b;
+		memset(&b, 0, sizeof(b));
+		cudaIpcMemHandle_t h;
+		cudaError_t e = cudaIpcGetMemHandle(&h, c->ranks[0].seg);
+		if(e != cudaSuccess) {
+			set_error("cudaIpcGetMemHandle failed: %s", cudaGetErrorString(e));
+			r = SNL_ERR_CUDA;
+		}
+		else {
+			static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+			memcpy(b.handle, &h, 64);
+			b.world = world;
+			b.W = W;
+			b.H = H;
+			b.magic = kBlobMagic;
+			memset(blob, 0, SNL_COMM_BLOB_BYTES);
+			memcpy(blob, &b, sizeof(b));
+		}
+	}
+	if(r) {
+		snl_comm_destroy(c);
+		return r;
+	}
+	*out = c;
+	return SNL_OK;
+}
+
+int snl_comm_attach(snl_scene *s, int rank, const unsigned char blob[SNL_COMM_BLOB_BYTES], snl_comm **out) {
+	SNL_REQUIRE(s && blob && out, SNL_ERR_INVALID, "null argument");
+	Blob b;
+	memcpy(&b, blob, sizeof(b));
+	SNL_REQUIRE(b.magic == kBlobMagic, SNL_ERR_INVALID, "not a snl_comm blob");
+	SNL_REQUIRE(rank > 0 && rank < b.world, SNL_ERR_INVALID, "rank %d outside 1..%d (rank 0 is the root)", rank, b.world - 1);
+	snl_comm *c = new snl_comm;
+	int r = comm_geometry(c, b.world, b.W, b.H);
+	CommRank cr;
+	cr.scene = s;
+	cr.rank = rank;
+	if(!r) {
+		cudaIpcMemHandle_t h;
+		memcpy(&h, b.handle, 64);
+		void *p = nullptr;
+		cudaError_t e = cudaSetDevice(s->device);
+		if(e == cudaSuccess)
+			e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+		if(e != cudaSuccess) {
+			set_error("cudaIpcOpenMemHandle failed: %s", cudaGetErrorString(e));
+			r = SNL_ERR_CUDA;
+		}
+		cr.seg = (unsigned char *)p;
+		cr.ipc = p != nullptr;
+	}
+	c->ranks.push_back(cr);
+	if(!r)
+		r = comm_rank_events(c->ranks[0]);
+	if(r) {
+		snl_comm_destroy(c);
+		return r;
+	}
+	*out = c;
+	return SNL_OK;
+}
+
+int snl_comm_create_local(snl_scene *const *scenes, int n, int W, int H, snl_comm **out) {
+	SNL_REQUIRE(scenes && out && n >= 1, SNL_ERR_INVALID, "bad argument");
+	for(int i = 0; i < n; i++) {
+		SNL_REQUIRE(scenes[i], SNL_ERR_INVALID, "null scene %d", i);
+		for(int j = 0; j < i; j++)
+			SNL_REQUIRE(scenes[i]->device != scenes[j]->device, SNL_ERR_INVALID, "scenes %d and %d share device %d", j, i,
+						scenes[i]->device);
+	}
+	snl_comm *c = new snl_comm;
+	int r = comm_geometry(c, n, W, H);
+	unsigned char *seg = nullptr;
+	if(!r)
+		r = alloc_segment(c, scenes[0], &seg);
+	for(int i = 0; i < n && !r; i++) {
+		CommRank cr;
+		cr.scene = scenes[i];
+		cr.rank = i;
+		cr.seg = seg;  // unified addressing: a peer-enabled device dereferences rank 0's pointer directly
+		c->ranks.push_back(cr);
+		if(i > 0) {
+			int can = 0;
+			cudaDeviceCanAccessPeer(&can, scenes[i]->device, scenes[0]->device);
+			if(!can) {
+				set_error("device %d cannot access device %d's memory (no peer path)", scenes[i]->device, scenes[0]->device);
+				r = SNL_ERR_UNSUPPORTED;
+				break;
+			}
+			cudaSetDevice(scenes[i]->device);
+			cudaError_t e = cudaDeviceEnablePeerAccess(scenes[0]->device, 0);
+			if(e == cudaErrorPeerAccessAlreadyEnabled)
+				cudaGetLastError();
+			else if(e != cudaSuccess) {
+				set_error("cudaDeviceEnablePeerAccess failed: %s", cudaGetErrorString(e));
+				r = SNL_ERR_CUDA;
+				break;
+			}
+		}
+		r = comm_rank_events(c->ranks.back());
+	}
+	if(!r)
+		r = comm_root_resources(c);
+	if(r) {
+		snl_comm_destroy(c);
+		return r;
+	}
+	*out = c;
+	return SNL_OK;
+}
+
+void snl_comm_destroy(snl_comm *c) {
+	if(!c)
+		return;
+	for(CommRank &r : c->ranks) {
+		if(!r.scene)
+			continue;
+		cudaSetDevice(r.scene->device);
+		cudaStreamSynchronize(r.scene->stream);
+		if(r.ev0)
+			cudaEventDestroy(r.ev0);
+		if(r.ev1)
+			cudaEventDestroy(r.ev1);
+		if(r.ipc && r.seg)
+			cudaIpcCloseMemHandle(r.seg);
+	}
+	if(!c->ranks.empty() && c->ranks[0].rank == 0 && c->ranks[0].scene) {
+		cudaSetDevice(c->ranks[0].scene->device);
+		for(int b = 0; b < kCommBands; b++) {
+			if(c->copyStream[b]) {
+				cudaStreamSynchronize(c->copyStream[b]);
+				cudaStreamDestroy(c->copyStream[b]);
+			}
+			if(c->copyEv[b])
+				cudaEventDestroy(c->copyEv[b]);
+		}
+		if(c->openEv)
+			cudaEventDestroy(c->openEv);
+		if(c->hStats)
+			cudaFreeHost(c->hStats);
+		if(c->ownsSegment && c->ranks[0].seg)
+			cudaFree(c->ranks[0].seg);
+	}
+	delete c;
+}
+
+int snl_comm_info(const snl_comm *c, int *world, int *W, int *H, int *localRanks) {
+	SNL_REQUIRE(c, SNL_ERR_INVALID, "null comm");
+	if(world)
+		*world = c->world;
+	if(W)
+		*W = c->W;
+	if(H)
+		*H = c->H;
+	if(localRanks)
+		*localRanks = (int)c->ranks.size();
+	return SNL_OK;
+}
+
+int snl_comm_frame(snl_comm *c, void **bgr8_dev, size_t *pitch) {
+	SNL_REQUIRE(c && bgr8_dev && c->seq > 0, SNL_ERR_STATE, "no frame rendered yet");
+	*bgr8_dev = c->ranks[0].seg + kCommCtlBytes + (size_t)((c->seq - 1) & 1u) * c->frameBytes;
+	if(pitch)
+		*pitch = c->pitch;
+	return SNL_OK;
+}
+
+int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_host, size_t hostPitch, snl_stats *stats) {
+	SNL_REQUIRE(c && cam, SNL_ERR_INVALID, "null argument");
+	SNL_REQUIRE(!bgr8_host || hostPitch >= (size_t)c->W * 3, SNL_ERR_INVALID, "host pitch too small");
+	const int W = c->W, H = c->H;
+	const unsigned seq = c->seq, slot = seq & 1u;
+	const int px = (W + 15) / 16, py = (H + 15) / 16;
+	const unsigned nPackets = (unsigned)(px * py);
+	bool isRoot = false;
+	for(CommRank &r : c->ranks) {
+		snl_scene *s = r.scene;
+		SNL_CUDA(cudaSetDevice(s->device));
+		SNL_REQUIRE(s->nGpuNodes > 0, SNL_ERR_STATE, "rank %d: no geometry", r.rank);
+		SNL_REQUIRE(!s->gVals[9], SNL_ERR_UNSUPPORTED, "gVals[9] supersampling is not available in snl_render_multi");
+		// the register-budget variant of k_render is picked on this rank's first frame by the single-GPU path
+		if(s->tune.choice < 0 || s->tuneW != W || s->tuneH != H) {
+			SNL_CUDA(s->dImage.reserve((size_t)W * 3 * H));
+			SNL_CUDA(cudaMemsetAsync(s->dCounters.ptr, 0, sizeof(Counters), s->stream));
+			SNL_TRY(render_local(s, cam, W, H, nullptr, 0, s->dImage.ptr, (size_t)W * 3, r.rank));
+			s->tuneW = W;
+			s->tuneH = H;
+		}
+		CommCtl *ctl = reinterpret_cast<CommCtl *>(r.seg);
+		unsigned char *frame = r.seg + kCommCtlBytes + (size_t)slot * c->frameBytes;
+		SNL_CUDA(cudaMemsetAsync(s->dCounters.ptr, 0, sizeof(Counters), s->stream));
+		SNL_CUDA(cudaEventRecord(r.ev0, s->stream));
+		SceneDev S;
+		RayGenParams g;
+		SNL_TRY(prepare_frame(s, cam, W, H, r.rank, S, g));
+		if(r.rank == 0) {
+			isRoot = true;
+			SNL_CUDA(launch_frame_open(ctl, seq, c->world, s->stream));
+			SNL_CUDA(cudaEventRecord(c->openEv, s->stream));
+			s->launches++;
+		}
+		const int variant = std::max(0, s->tune.choice);
+		const int ctas = s->smCount * render_ctas_per_sm(S, variant);
+		DynCtl d;
+		d.cursor = &ctl->cursor[slot];
+		d.bandDone = ctl->bandDone[slot];
+		d.ready = &ctl->ready[slot];
+		d.readyVal = seq + 1u;
+		d.nPackets = nPackets;
+		// batches of a few packets while there are plenty per resident CTA, single packets once the GPUs would starve
+		const unsigned perCta = nPackets / std::max(1u, (unsigned)(ctas * c->world));
+		d.batch = perCta >= 16 ? 4u : perCta >= 8 ? 2u : 1u;
+		d.nBatches = (nPackets + d.batch - 1) / d.batch;
+		d.rowsPerBand = (unsigned)c->rowsPerBand;
+		d.error = &ctl->error;
+		SNL_CUDA(launch_render(S, s->originPre.set(), g, W, H, nullptr, 0, frame, c->pitch, variant, s->stream, 0, -1, &d, ctas));
+		SNL_CUDA(launch_frame_publish(ctl, s->dCounters.ptr, seq, r.rank, s->stream));
+		s->launches += 2;
+		SNL_CUDA(cudaEventRecord(r.ev1, s->stream));
+		if(r.rank == 0) {
+			if(bgr8_host) {
+				for(int b = 0; b < c->nBands; b++) {
+					const int r0 = b * c->rowsPerBand, r1 = std::min(py, (b + 1) * c->rowsPerBand);
+					const int y0 = r0 * 16, y1 = std::min(H, r1 * 16);
+					cudaStream_t st = c->copyStream[b];
+					SNL_CUDA(cudaStreamWaitEvent(st, c->openEv, 0));
+					SNL_CUDA(launch_wait_counter(&ctl->bandDone[slot][b], (unsigned)((r1 - r0) * px), &ctl->error, st));
+					SNL_CUDA(cudaMemcpy2DAsync(bgr8_host + (size_t)y0 * hostPitch, hostPitch, frame + (size_t)y0 * c->pitch, c->pitch,
+											   (size_t)W * 3, y1 - y0, cudaMemcpyDeviceToHost, st));
+					SNL_CUDA(cudaEventRecord(c->copyEv[b], st));
+					SNL_CUDA(cudaStreamWaitEvent(s->stream, c->copyEv[b], 0));
+					s->launches++;
+				}
+			}
+			// every rank has published = every packet of the frame is stored and every counter is in
+			SNL_CUDA(launch_wait_counter(&ctl->statsArrived[slot], (unsigned)c->world, &ctl->error, s->stream));
+			s->launches++;
+			SNL_CUDA(cudaMemcpyAsync(c->hStats, ctl->stats[slot], 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
+			SNL_CUDA(cudaMemcpyAsync(c->hStats + 8, &ctl->error, sizeof(unsigned), cudaMemcpyDeviceToHost, s->stream));
+		}
+	}
+	c->seq++;
+	float ms = 0.0f;
+	for(CommRank &r : c->ranks) {
+		SNL_CUDA(cudaSetDevice(r.scene->device));
+		SNL_CUDA(cudaStreamSynchronize(r.scene->stream));
+		float m = 0.0f;
+		if(cudaEventElapsedTime(&m, r.ev0, r.ev1) == cudaSuccess)
+			ms = std::max(ms, m);
+	}
+	c->lastMs = ms;
+	if(isRoot)
+		SNL_REQUIRE(*(const unsigned *)(c->hStats + 8) == 0, SNL_ERR_STATE,
+					"snl_render_multi: a rank did not arrive within the time-out (every rank must call it once per frame)");
+	if(stats) {
+		memset(stats, 0, sizeof(*stats));
+		Counters k;
+		if(isRoot)
+			memcpy(&k, c->hStats, sizeof(k));  // summed over the ranks
+		else {                                   // this rank's share
+			snl_scene *s = c->ranks[0].scene;
+			SNL_CUDA(cudaMemcpy(&k, s->dCounters.ptr, sizeof(k), cudaMemcpyDeviceToHost));
+		}
+		stats->primary = k.primary;
+		stats->shadow = k.shadow;
+		stats->reflection = k.reflection;
+		stats->reflection_shadow = k.reflection_shadow;
+		stats->transparency = k.transparency;
+		stats->rays = k.primary + k.shadow + k.reflection + k.reflection_shadow + k.transparency;
+		stats->node_visits = k.node_visits;
+		stats->tri_tests = k.tri_tests;
+		stats->gtri_tests = k.gtri_tests;
+		stats->kernel_ms = ms;
+	}
+	return SNL_OK;
+}
+
+}  // extern "C"

@@ -1226,6 +1226,38 @@ __device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet or
 		level_compose(S, f, f.ar, f.ag, f.ab, outr, outg, outb);
 }
 
+// ---- cross-GPU signalling (snl_comm.cu): system-scope waits with a time-out so that a missing peer ends in an error
+// status instead of a hung device ------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
+	unsigned v;
+	asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+	return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
+	asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+	unsigned long long t;
+	asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+	return t;
+}
+enum : unsigned long long { kWaitTimeoutNs = 8000000000ull };
+// waits until *p >= v (ge) or *p == v; false = timed out (and *err set)
+template <bool GE> __device__ __forceinline__ bool wait_sys(const unsigned *p, unsigned v, unsigned *err) {
+	const unsigned long long t0 = global_timer_ns();
+	for(;;) {
+		const unsigned cur = ld_acquire_sys(p);
+		if(GE ? cur >= v : cur == v)
+			return true;
+		if(global_timer_ns() - t0 > kWaitTimeoutNs) {
+			if(err)
+				st_release_sys(err, 1u);
+			return false;
+		}
+		__nanosleep(100);
+	}
+}
+
 // CTA-level aggregation of the per-lane ray counters into the scene's global counters.
 __device__ __forceinline__ void flush_counts(const SceneDev &S, const PacketCounts &pc, const TravCount &tc) {
 	__shared__ unsigned sh[8];

@@ -2,6 +2,8 @@
 #include "snl_device.cuh"
 #include "snl_kernels.h"
 
+#include <cstring>
+
 namespace snl {
 
 // Per-origin records, one launch per origin and frame: Triangle::Collide's sharedOrigin precomputation
@@ -190,38 +192,19 @@ __device__ __forceinline__ unsigned conv_channel(float c) {
 // MINB: resident CTAs per SM the register allocation aims for. 4 (64 registers) suits scenes whose hot set sits in L1;
 // 5 (48 registers, a few more spills) hides more latency on large scenes: +1.9 % on sponza_like, -2 % on feline.
 // The scene picks per workload by timing both on its first frames (snl_capi.cu render_common).
-template <int FLAGS, bool SUPER, int MINB>
-__global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreSet pre, RayGenParams g, int W, int H,
-												 int packetsX, const int4 *__restrict__ packets,
-												 unsigned char *__restrict__ out, size_t pitch, int firstPacket) {
-	int px0, py0, cw, ch;
-	const int packet = blockIdx.x + firstPacket;
-	if(packets) {
-		const int4 p = packets[packet];
-		px0 = p.x;
-		py0 = p.y;
-		cw = p.z;
-		ch = p.w;
-	}
-	else {
-		px0 = (packet % packetsX) * 16;
-		py0 = (packet / packetsX) * 16;
-		cw = min(16, W - px0);
-		ch = min(16, H - py0);
-	}
+// One packet of RenderTask::Work: traces and shades the 16x16 pixels at (px0, py0) and leaves their bytes in `tile`
+// (SUPER: stores them itself). All 256 threads of the CTA call it.
+template <int FLAGS, bool SUPER>
+__device__ __forceinline__ void render_packet(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int px0, int py0, int cw,
+											  int ch, unsigned char *__restrict__ out, size_t pitch, unsigned char *tile,
+											  PacketCounts &pc, TravCount &tc) {
 	const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-	PacketCounts pc = {0, 0, 0, 0, 0};
-	TravCount tc = {0, 0, 0};
-	constexpr bool VSTORE = !SUPER;
-	__shared__ __align__(16) unsigned char tile[VSTORE ? 16 * 48 : 16];
 	// the plain kernel settles the per-packet light cull's ray accounting at its end instead of with barriers per level
 	constexpr int LFLAGS = (FLAGS == 0 && !SUPER) ? 4 : FLAGS;
 	if(LFLAGS == 4 && S.cullMask) {
 		cull_state_init();
 		__syncthreads();
 	}
-	if(S.hasUber)
-		packet_vote_init();
 	// Like the reference we trace the whole 16x16 packet even when it overhangs the image or the tile
 	// (src/render.cpp:112-115): overhanging lanes take part in the 16-lane shading blocks and in the packet-wide
 	// selector.All() test of the reflection pass (src/scene_trace.cpp:615-617), and TreeStats counts them.
@@ -255,8 +238,8 @@ __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreS
 			b = (b + 0.1f) * S.tint[2];
 		}
 		const unsigned cb = conv_channel(b), cg = conv_channel(gg), cr = conv_channel(r);
-		if(VSTORE) {
-			// stage the packet's 16 x 48 bytes and write them as 16-byte vectors below: one 16-byte store per 5.3 pixels
+		if(!SUPER) {
+			// stage the packet's 16 x 48 bytes; store_tile() writes them as 16-byte vectors: one store per 5.3 pixels
 			// instead of three 1-byte stores per pixel (what matters when `out` is rank 0's frame behind NVLink)
 			unsigned char *t = tile + ty * 48 + tx * 3;
 			t[0] = (unsigned char)cb;
@@ -273,9 +256,13 @@ __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreS
 	}
 	if(LFLAGS == 4 && S.cullMask)
 		cull_resolve(S, pc);
-	flush_counts(S, pc, tc);  // its barriers also publish `tile`
-	if(VSTORE && threadIdx.x < 48) {
-		const int row = threadIdx.x / 3, part = threadIdx.x - row * 3;  // 3 x 16 bytes per packet row
+}
+
+// The staged packet -> frame, 3 x 16 bytes per packet row (after a CTA barrier that follows render_packet).
+__device__ __forceinline__ void store_tile(const unsigned char *tile, int px0, int py0, int cw, int ch,
+										   unsigned char *__restrict__ out, size_t pitch) {
+	if(threadIdx.x < 48) {
+		const int row = threadIdx.x / 3, part = threadIdx.x - row * 3;
 		if(row < ch) {
 			unsigned char *dst = out + (size_t)(py0 + row) * pitch + (size_t)px0 * 3 + part * 16;
 			const unsigned char *src = tile + row * 48 + part * 16;
@@ -286,6 +273,74 @@ __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreS
 					dst[i] = src[i];
 		}
 	}
+}
+
+// DYN = false: one packet per CTA (blockIdx + firstPacket). DYN = true: persistent CTAs that fetch packet batches from
+// the frame's shared cursor and count every stored packet off in its row band (multi-GPU frame, snl_comm.cu); a separate
+// instantiation because the loop costs the static kernel registers (measured: +2 % frame time when folded into one).
+template <int FLAGS, bool SUPER, int MINB, bool DYN>
+__global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreSet pre, RayGenParams g, int W, int H,
+												 int packetsX, const int4 *__restrict__ packets,
+												 unsigned char *__restrict__ out, size_t pitch, int firstPacket, const DynCtl ctl) {
+	PacketCounts pc = {0, 0, 0, 0, 0};
+	TravCount tc = {0, 0, 0};
+	__shared__ __align__(16) unsigned char tile[SUPER ? 16 : 16 * 48];
+	if(S.hasUber)
+		packet_vote_init();
+	if(!DYN) {
+		int px0, py0, cw, ch;
+		const int packet = blockIdx.x + firstPacket;
+		if(packets) {
+			const int4 p = packets[packet];
+			px0 = p.x;
+			py0 = p.y;
+			cw = p.z;
+			ch = p.w;
+		}
+		else {
+			px0 = (packet % packetsX) * 16;
+			py0 = (packet / packetsX) * 16;
+			cw = min(16, W - px0);
+			ch = min(16, H - py0);
+		}
+		render_packet<FLAGS, SUPER>(S, pre, g, px0, py0, cw, ch, out, pitch, tile, pc, tc);
+		flush_counts(S, pc, tc);  // its barriers also publish `tile`
+		if(!SUPER)
+			store_tile(tile, px0, py0, cw, ch, out, pitch);
+		return;
+	}
+	__shared__ unsigned sBatch;
+	if(threadIdx.x == 0) {
+		// the frame slot is opened by rank 0 (k_frame_open) once every rank has left the frame that used it before
+		sBatch = wait_sys<false>(ctl.ready, ctl.readyVal, ctl.error) ? 0u : 0xffffffffu;
+	}
+	for(;;) {
+		__syncthreads();
+		if(threadIdx.x == 0 && sBatch != 0xffffffffu) {
+			const unsigned long long b = atomicAdd_system(ctl.cursor, 1ull);
+			sBatch = b < ctl.nBatches ? (unsigned)b : 0xfffffffeu;
+		}
+		__syncthreads();
+		const unsigned b = sBatch;
+		if(b >= ctl.nBatches)
+			break;
+		const unsigned first = b * ctl.batch, count = min(ctl.batch, ctl.nPackets - first);
+		for(unsigned k = 0; k < count; k++) {
+			const int packet = (int)(first + k);
+			const int px0 = (packet % packetsX) * 16, py0 = (packet / packetsX) * 16;
+			const int cw = min(16, W - px0), ch = min(16, H - py0);
+			render_packet<FLAGS, SUPER>(S, pre, g, px0, py0, cw, ch, out, pitch, tile, pc, tc);
+			__syncthreads();
+			if(!SUPER)
+				store_tile(tile, px0, py0, cw, ch, out, pitch);
+			__syncthreads();  // every pixel of the packet is on its way, `tile` is free again
+			if(threadIdx.x == 0) {
+				__threadfence_system();
+				atomicAdd_system(ctl.bandDone + min((unsigned)(py0 >> 4) / ctl.rowsPerBand, (unsigned)kCommBands - 1u), 1u);
+			}
+		}
+	}
+	flush_counts(S, pc, tc);
 }
 
 // ---- launch wrappers ------------------------------------------------------------------------------------------
@@ -354,27 +409,108 @@ cudaError_t launch_raytrace(const SceneDev &S, const PreSet &pre, const float *o
 }
 
 cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, const int4 *packets,
-						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st, int first, int count) {
+						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st, int first, int count,
+						  const DynCtl *dyn, int persistentCtas) {
 	const int px = (W + 15) / 16, py = (H + 15) / 16;
 	const int all = packets ? nPackets : px * py;
-	const int grid = count < 0 ? all - first : count;
-	if(grid <= 0 || first < 0 || first + grid > all)
+	int grid = count < 0 ? all - first : count;
+	DynCtl ctl;
+	memset(&ctl, 0, sizeof(ctl));
+	if(dyn) {  // persistent CTAs fetching packet batches from dyn->cursor
+		ctl = *dyn;
+		grid = persistentCtas;
+		first = 0;
+	}
+	if(grid <= 0 || first < 0 || (!dyn && first + grid > all))
 		return cudaSuccess;
 	const int MB = SNL_RENDER_MIN_BLOCKS;
-	if(S.instances)  // Scene<DBVH>: simple shading only, so no transparency; supersampling is refused by the caller
-		k_render<2, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first);
+#define SNL_LAUNCH_RENDER(F, SUP, B, D) k_render<F, SUP, B, D><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first, ctl)
+	if(dyn) {  // full frames without supersampling only (snl_render_multi checks)
+		if(packets || S.gvSuper)
+			return cudaErrorInvalidValue;
+		if(S.instances)
+			SNL_LAUNCH_RENDER(2, false, MB, true);
+		else if(S.hasTransp)
+			SNL_LAUNCH_RENDER(1, false, MB, true);
+		else if(variant == 1)
+			SNL_LAUNCH_RENDER(0, false, MB + 1, true);
+		else
+			SNL_LAUNCH_RENDER(0, false, MB, true);
+	}
+	else if(S.instances)  // Scene<DBVH>: simple shading only, so no transparency; supersampling is refused by the caller
+		SNL_LAUNCH_RENDER(2, false, MB, false);
 	else if(S.hasTransp) {
 		if(S.gvSuper)
-			k_render<1, true, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first);
+			SNL_LAUNCH_RENDER(1, true, MB, false);
 		else
-			k_render<1, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first);
+			SNL_LAUNCH_RENDER(1, false, MB, false);
 	}
 	else if(S.gvSuper)
-		k_render<0, true, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first);
+		SNL_LAUNCH_RENDER(0, true, MB, false);
 	else if(variant == 1)
-		k_render<0, false, MB + 1><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first);
+		SNL_LAUNCH_RENDER(0, false, MB + 1, false);
 	else
-		k_render<0, false, MB><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first);
+		SNL_LAUNCH_RENDER(0, false, MB, false);
+#undef SNL_LAUNCH_RENDER
+	return cudaGetLastError();
+}
+
+int render_ctas_per_sm(const SceneDev &S, int variant) {
+	const int MB = SNL_RENDER_MIN_BLOCKS;
+	return (!S.instances && !S.hasTransp && !S.gvSuper && variant == 1) ? MB + 1 : MB;
+}
+
+// ---- multi-GPU frame protocol (CommCtl in rank 0's memory, see snl_comm.cu) ------------------------------------
+__global__ void k_frame_open(CommCtl *ctl, unsigned seq, int world) {
+	const unsigned slot = seq & 1u;
+	// the slot was last used by frame seq - 2: nobody may still be fetching from / reporting to it
+	if((int)threadIdx.x < world && seq >= 2)
+		wait_sys<true>(&ctl->rankDone[threadIdx.x], seq - 1u, &ctl->error);
+	__syncwarp();
+	if(threadIdx.x == 0) {
+		ctl->cursor[slot] = 0ull;
+		ctl->statsArrived[slot] = 0u;
+	}
+	if(threadIdx.x < 8)
+		ctl->stats[slot][threadIdx.x] = 0ull;
+	if(threadIdx.x < kCommBands)
+		ctl->bandDone[slot][threadIdx.x] = 0u;
+	__syncwarp();
+	if(threadIdx.x == 0) {
+		__threadfence_system();
+		st_release_sys(&ctl->ready[slot], seq + 1u);
+	}
+}
+
+__global__ void k_frame_publish(CommCtl *ctl, const Counters *local, unsigned seq, int rank) {
+	const unsigned slot = seq & 1u;
+	if(threadIdx.x < 8) {
+		const unsigned long long v = reinterpret_cast<const unsigned long long *>(local)[threadIdx.x];
+		if(v)
+			atomicAdd_system(&ctl->stats[slot][threadIdx.x], v);
+	}
+	__syncwarp();
+	if(threadIdx.x == 0) {
+		__threadfence_system();
+		atomicAdd_system(&ctl->statsArrived[slot], 1u);
+		st_release_sys(&ctl->rankDone[rank], seq + 1u);
+	}
+}
+
+__global__ void k_wait_counter(const unsigned *counter, unsigned expected, unsigned *error) {
+	wait_sys<true>(counter, expected, error);
+}
+
+cudaError_t launch_frame_open(CommCtl *ctl, unsigned seq, int world, cudaStream_t st) {
+	k_frame_open<<<1, 32, 0, st>>>(ctl, seq, world);
+	return cudaGetLastError();
+}
+cudaError_t launch_frame_publish(CommCtl *ctl, const Counters *local, unsigned seq, int rank, cudaStream_t st) {
+	k_frame_publish<<<1, 32, 0, st>>>(ctl, local, seq, rank);
+	return cudaGetLastError();
+}
+cudaError_t launch_wait_counter(const unsigned *counter, unsigned expected, unsigned *error, cudaStream_t st) {
+	k_wait_counter<<<1, 1, 0, st>>>(counter, expected, error);
 	return cudaGetLastError();
 }
 

@@ -125,6 +125,14 @@ struct snl_scene {
 	snl::DevBuf<float2> wfSdot;
 	snl::DevBuf<unsigned> wfRq, wfSq, wfOccl, wfCount;
 	snl::DevBuf<snl::PreSet> wfLightSets;
+	int tuneW = 0, tuneH = 0;  // frame size snl_render_multi last ran the variant pick for
 	int smCount = 0;
 	int fused = 1;  // 0 (SNL_WAVEFRONT=1): wavefront pipeline for frames with the reflection bounce
 };
+
+namespace snl {
+// host-side helpers shared by snl_capi.cu and snl_comm.cu
+int prepare_frame(snl_scene *s, const snl_camera *cam, int W, int H, int rank, SceneDev &S, RayGenParams &g);
+int render_local(snl_scene *s, const snl_camera *cam, int W, int H, const int *tiles, int nTiles, unsigned char *dOut,
+				  size_t pitch, int rank);
+}  // namespace snl

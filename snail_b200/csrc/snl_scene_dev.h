@@ -37,6 +37,32 @@ struct SceneDev {
 	Counters *counters;
 };
 
+// Multi-GPU frame (snl_comm.cu): control block at the start of the segment rank 0 shares with its peers (CUDA IPC or
+// peer access), all fields updated with system-scope atomics / release stores. Two frame slots alternate.
+enum { kCommBands = 8, kCommRanks = 16, kCommCtlBytes = 4096 };
+struct CommCtl {
+	unsigned long long cursor[2];               // next packet batch of the frame in this slot
+	unsigned long long stats[2][8];             // Counters of the frame summed over the ranks
+	unsigned bandDone[2][kCommBands];           // packets completed per row band
+	unsigned ready[2];                          // seq + 1 once the slot has been opened for frame seq
+	unsigned statsArrived[2];
+	unsigned rankDone[kCommRanks];              // frames completed by each rank (seq + 1)
+	unsigned error;                             // a wait timed out somewhere
+};
+static_assert(sizeof(CommCtl) <= kCommCtlBytes, "CommCtl must fit its page");
+
+// k_render's work source: cursor == null -> one packet per CTA (blockIdx + firstPacket); else persistent CTAs that fetch
+// batches of packets from the shared cursor and report every finished packet to its band's counter.
+struct DynCtl {
+	unsigned long long *cursor;
+	unsigned *bandDone;     // [kCommBands] of this frame's slot
+	const unsigned *ready;  // fetch only once *ready == readyVal
+	unsigned readyVal;
+	unsigned nBatches, batch, nPackets;
+	unsigned rowsPerBand;   // packet rows per band
+	unsigned *error;
+};
+
 // Wavefront pipeline state for one frame (snl_wavefront.cu). NL = packets * 256 lanes; arrays are lane-indexed
 // (lane = packet * 256 + thread) unless noted, so the shading kernels keep the reference's packet / quad structure
 // while the traversal kernels pull rays from compacted queues.

@@ -4,9 +4,10 @@ src/render.cpp:140-211 per-tile output). One process per GPU (torch.distributed)
 are partitioned, secondary rays never leave the GPU that spawned them.
 
 Two compose paths:
-  * "p2p"  — rank 0 owns the frame (snl_frame_create), every other rank maps it through CUDA IPC
-             (snl_frame_open) and k_render stores its pixels straight into rank 0's HBM over NVLink/NVSwitch:
-             compute and gather are ONE kernel, no staging buffer, no collective on the data path.
+  * "p2p"  — snl_comm_* / snl_render_multi (snail_b200/csrc/snl_comm.cu, C++ behind the C ABI): rank 0 owns the
+             frame, every other rank maps it through CUDA IPC and its persistent k_render stores packets straight
+             into rank 0's HBM over NVLink/NVSwitch, fetching them from a shared cursor: compute and gather are ONE
+             kernel, no staging buffer, no collective on the data path. This module only bootstraps it.
   * "gather" — every rank packs its tiles into a contiguous buffer, torch.distributed gathers the buffers on
              rank 0 (NCCL on GPUs, gloo in the CPU tests), rank 0 scatters them into the frame.
 """
@@ -119,58 +120,54 @@ def reduce_stats(dist, stats: dict, device=None) -> dict:
 
 class Farm:
     """Render() over the ranks of one box: the counterpart of the reference's server loop (src/server.cpp:266-420)
-    with `dist` = an initialised torch.distributed (NCCL) process group and `scene` = this rank's snail_b200.Scene
-    holding a replica of the scene. compose = "p2p" (default; peer stores into rank 0's frame) or "gather"."""
+    with `dist` = an initialised torch.distributed process group (used ONLY to hand rank 0's 96-byte bootstrap blob to
+    the other ranks, and by the "gather" compose) and `scene` = this rank's snail_b200.Scene holding a replica of the
+    scene. compose = "p2p" (default): a thin caller of snl_comm_* / snl_render_multi (C++ behind the ABI: shared
+    cursor, peer stores into rank 0's frame, in-stream completion, banded device->host copy; no per-frame host
+    collective, two frame slots so a rank can start frame k+1 while rank 0 still reads frame k). compose = "gather":
+    static tile split + torch.distributed gather of packed tiles (the NCCL collective north_star words; kept as the
+    cross-check and for boxes without peer access)."""
 
     def __init__(self, scene, dist, W: int, H: int, compose: str = "p2p", seed: int = 1):
+        from .api import Comm
         self.scene, self.dist, self.W, self.H, self.compose = scene, dist, W, H, compose
         self.rank, self.world = dist.get_rank(), dist.get_world_size()
-        self.tiles = tiles_for_rank(W, H, self.rank, self.world, seed) if self.world > 1 else None
         self.seed = seed
-        self.image = None
+        self.image = self.comm = self.tiles = None
         if compose == "p2p":
-            handle = [None]
+            blob = [None]
             if self.rank == 0:
-                self.frame, handle[0] = scene.frame_create(W, H)
-            dist.broadcast_object_list(handle, src=0)
+                self.comm, blob[0] = Comm.root(scene, self.world, W, H)
+            dist.broadcast_object_list(blob, src=0)
             if self.rank != 0:
-                self.frame = scene.frame_open(handle[0])
+                self.comm = Comm.attach(scene, self.rank, blob[0])
         else:
             import torch
+            self.tiles = tiles_for_rank(W, H, self.rank, self.world, seed) if self.world > 1 else None
             self.image = torch.zeros((H, W, 3), dtype=torch.uint8, device=torch.device("cuda", scene.device))
-            self.frame = self.image.data_ptr()
 
-    def render_async(self, cam):
-        """Launches this rank's tiles (asynchronous on the scene's stream)."""
-        self.scene.render_dev(cam, self.W, self.H, self.frame, self.W * 3, tiles=self.tiles, rank=self.rank)
-
-    def finish(self):
-        """Waits for this rank's kernels, completes the compose; returns this rank's stats."""
-        st = self.scene.sync()
-        if self.image is not None:
-            gather_frame(self.dist, self.image, self.W, self.H, self.rank, self.world, self.seed)
-        self.dist.barrier()  # p2p: every rank's stores have landed in rank 0's frame
-        return st
-
-    def render(self, cam, out=None):
-        """Whole frame: returns (image on rank 0 else None, TreeStats summed over the ranks)."""
+    def render(self, cam, out=None, host=True):
+        """Whole frame, collective. Returns (image on rank 0 else None, TreeStats: summed over the ranks on rank 0)."""
+        if self.comm is not None:
+            return self.comm.render(cam, out=out, host=host)
         import torch
-        self.render_async(cam)
-        st = self.finish()
+        self.scene.render_dev(cam, self.W, self.H, self.image.data_ptr(), self.W * 3, tiles=self.tiles, rank=self.rank)
+        st = self.scene.sync()
+        gather_frame(self.dist, self.image, self.W, self.H, self.rank, self.world, self.seed)
         total = reduce_stats(self.dist, st, device=torch.device("cuda", self.scene.device))
         img = None
-        if self.rank == 0:
-            img = self.scene.frame_read(self.frame, self.W, self.H, out=out)
+        if self.rank == 0 and host:
+            img = self.scene.frame_read(self.image.data_ptr(), self.W, self.H, out=out)
         return img, total
 
     def close(self):
         self.dist.barrier()
-        if self.compose == "p2p":
+        if self.comm is not None:
             if self.rank != 0:
-                self.scene.frame_close(self.frame)
+                self.comm.close()  # unmap before the owner frees the segment
             self.dist.barrier()
             if self.rank == 0:
-                self.scene.frame_close(self.frame)
+                self.comm.close()
 
 
 def decode_farm_tiles(data: np.ndarray, coords, offsets, W: int, H: int, out: np.ndarray | None = None) -> np.ndarray:

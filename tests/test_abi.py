@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol(sb):
     L = sb.load_library()
     for name in header_symbols():
         assert hasattr(L, name), f"{name} declared in include/snail_b200.h but not exported"
-    assert L.snl_abi_version() == 2
+    assert L.snl_abi_version() == 3
 
 
 def test_counters_build_exports_the_same_abi(sb):
