@@ -156,6 +156,14 @@ int snl_scene_set_lights(snl_scene *, const snl_light *lights, int nLights, cons
  * (src/render.cpp:71-110). [5] (stats heat-map) returns SNL_ERR_UNSUPPORTED. */
 int snl_set_options(snl_scene *, const int gVals[16]);
 
+/* Reflection bounces followed when gVals[7] is on. 1 (default) = the reference: `cache.reflections < 1`
+ * (src/scene_trace.cpp:454-460) lets the bounce pass shade and light its hits but not bounce again. 2 = that condition
+ * relaxed to `< 2` (BASELINE config 5, "reflection depth 2"): BEYOND the reference, compared in the tests with the
+ * reference copy oracle/build_ref.sh patches the same way (oracle/_ref/libsnailref_depth2.so). Plain scenes only
+ * (instanced scenes, transparent materials and gVals[9] return SNL_ERR_UNSUPPORTED at render time); snl_raytrace keeps
+ * depth 1. */
+int snl_set_reflection_depth(snl_scene *, int depth);
+
 /* Host ingest + SAH builder (host side of the path): BaseScene::LoadWavefrontObj
  * (src/formats/wavefront_obj.cpp:66-200), FlipNormals/GenNormals (src/base_scene.cpp:326-335,517-529),
  * BVH::Construct (src/bvh/tree.cpp:293-328), LoadMaterialDescs/LoadTextures/MakeMaterials

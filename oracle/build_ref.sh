@@ -5,6 +5,10 @@
 #
 #   oracle/_ref/libsnailref_sse.so     veclib SSE back-end (rcpps/rsqrtps + 1 NR)  -> timed CPU baseline
 #   oracle/_ref/libsnailref_scalar.so  veclib scalar back-end (exact 1/x, 1/sqrt)   -> canonical oracle
+#   oracle/_ref/libsnailref_depth2.so  the scalar build with `cache.reflections < 1` relaxed to `< 2` (generated copy of
+#                                      src/scene_trace.cpp under gen-depth2/): comparison for snl_set_reflection_depth(2)
+#   oracle/_ref/libsnailref_b200adapter.so  the scalar build + oracle/ref_adapter.cpp: the product's include/scene_b200.h
+#                                      compiled inside the reference, linked with libsnail_b200.so (adapter test only)
 #   oracle/_ref/scenes/, oracle/_ref/data/  copies of the reference's scene/texture ASSETS (not sources)
 #
 # Two generated headers (build artefacts, never committed) make the in-place sources build with g++:
@@ -43,6 +47,14 @@ if old != new:
     open(sys.argv[2], 'w').write(new)
 EOF
 
+# depth-2 variant (BASELINE config 5 "reflection depth 2" is beyond the reference's own cap): the ONE condition
+# `cache.reflections < 1` (src/scene_trace.cpp:454) relaxed to `< 2` in a generated copy of that translation unit
+mkdir -p "$OUT/gen-depth2"
+sed 's/cache\.reflections < 1/cache.reflections < 2/' "$REF/src/scene_trace.cpp" > "$OUT/gen-depth2/scene_trace.cpp.tmp"
+grep -q 'cache.reflections < 2' "$OUT/gen-depth2/scene_trace.cpp.tmp" || { echo "build_ref: depth-2 patch did not apply" >&2; exit 1; }
+cmp -s "$OUT/gen-depth2/scene_trace.cpp.tmp" "$OUT/gen-depth2/scene_trace.cpp" 2>/dev/null || mv "$OUT/gen-depth2/scene_trace.cpp.tmp" "$OUT/gen-depth2/scene_trace.cpp"
+rm -f "$OUT/gen-depth2/scene_trace.cpp.tmp"
+
 cp -u "$REF"/scenes/*.obj "$REF"/scenes/*.mtl "$OUT/scenes/" 2>/dev/null || true
 cp -u "$REF"/data/*.png "$OUT/data/" 2>/dev/null || true
 
@@ -61,12 +73,16 @@ BASE="-std=c++2a -O3 -msse2 -ffp-contract=off -fPIC -fpermissive -w -fno-strict-
 COMMON="$BASE -I$REF/src -include $OUT/gen/rtbase_math.h -D'ASSERT_EQ(a,b)=ASSERT((a)==(b))'"
 FWKFLAGS="$BASE -DFATAL=FWK_FATAL"
 
+# the adapter library needs the product library to link against
+ADAPTER=""
+[ -f "$HERE/../snail_b200/libsnail_b200.so" ] && ADAPTER="$OUT/libsnailref_b200adapter.so"
+
 MK="$OUT/Makefile.gen"
 {
 	echo "CXX=g++"
 	echo "COMMON=$(echo $COMMON)"
 	echo "FWKFLAGS=$(echo $FWKFLAGS)"
-	echo "all: $OUT/libsnailref_sse.so $OUT/libsnailref_scalar.so"
+	echo "all: $OUT/libsnailref_sse.so $OUT/libsnailref_scalar.so $OUT/libsnailref_depth2.so $ADAPTER"
 	FWK_OBJS=""
 	for tu in $FWK_TUS; do
 		o="$OUT/obj/fwk/$(echo $tu | tr / _).o"
@@ -94,6 +110,25 @@ MK="$OUT/Makefile.gen"
 		done
 		echo "$OUT/libsnailref_$variant.so: $OBJS $FWK_OBJS"
 		echo "	\$(CXX) -shared -o \$@ \$^ -lpthread -Wl,--no-undefined"
+		if [ $variant = scalar ]; then
+			# the scalar build with scene_trace.cpp replaced by its depth-2 copy
+			o="$OUT/obj/depth2/scene_trace.o"
+			echo "$o: $OUT/gen-depth2/scene_trace.cpp $OUT/gen/rtbase_math.h $OUT/gen-scalar/veclib.h"
+			echo "	@mkdir -p \$(dir \$@)"
+			echo "	\$(CXX) \$(COMMON) $VINC -c \$< -o \$@"
+			echo "$OUT/libsnailref_depth2.so: $o $(echo $OBJS | tr ' ' '\n' | grep -v '/scene_trace.o$' | tr '\n' ' ') $FWK_OBJS"
+			echo "	\$(CXX) -shared -o \$@ \$^ -lpthread -Wl,--no-undefined"
+		fi
+		if [ $variant = scalar ] && [ -n "$ADAPTER" ]; then
+			# the product's reference-side adapter (include/scene_b200.h) compiled inside the reference and linked with
+			# libsnail_b200.so into a library of its own; render.o is left out: ref_adapter.cpp includes src/render.cpp
+			o="$OUT/obj/$variant/ref_adapter.o"
+			echo "$o: $HERE/ref_adapter.cpp $HERE/../include/scene_b200.h $HERE/../include/snail_b200.h $REF/src/render.cpp $OUT/gen/rtbase_math.h"
+			echo "	@mkdir -p \$(dir \$@)"
+			echo "	\$(CXX) \$(COMMON) $VINC -I$HERE/../include -c \$< -o \$@"
+			echo "$ADAPTER: $o $(echo $OBJS | tr ' ' '\n' | grep -v '/render.o$' | tr '\n' ' ') $FWK_OBJS $HERE/../snail_b200/libsnail_b200.so"
+			echo "	\$(CXX) -shared -o \$@ $o $(echo $OBJS | tr ' ' '\n' | grep -v '/render.o$' | tr '\n' ' ') $FWK_OBJS -L$HERE/../snail_b200 -lsnail_b200 -Wl,-rpath,'\$\$ORIGIN/../../snail_b200' -lpthread -Wl,--no-undefined"
+		fi
 	done
 } > "$MK"
 

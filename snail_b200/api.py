@@ -17,7 +17,7 @@ LIB_COUNTERS_PATH = os.path.join(HERE, "libsnail_b200_counters.so")
 # names every include/snail_b200.h declaration must resolve to (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
     "snl_last_error", "snl_abi_version", "snl_device_count", "snl_scene_create", "snl_scene_destroy",
-    "snl_scene_set_geometry", "snl_scene_set_materials", "snl_scene_set_lights", "snl_set_options",
+    "snl_scene_set_geometry", "snl_scene_set_materials", "snl_scene_set_lights", "snl_set_options", "snl_set_reflection_depth",
     "snl_scene_load_obj", "snl_scene_counts", "snl_scene_copy_host_bvh", "snl_scene_bbox", "snl_trace_primary",
     "snl_trace_rays", "snl_trace_shadow", "snl_raytrace", "snl_render", "snl_render_dev", "snl_render_farm", "snl_scene_sync",
     "snl_scene_launch_count", "snl_scene_render_variant", "snl_scene_stream", "snl_host_scene_load_obj", "snl_host_scene_free",
@@ -130,6 +130,7 @@ def load_library(counters: bool = False) -> C.CDLL:
     L.snl_scene_set_materials.argtypes = [vp, vp, i, vp, i]
     L.snl_scene_set_lights.argtypes = [vp, vp, i, vp]
     L.snl_set_options.argtypes = [vp, vp]
+    L.snl_set_reflection_depth.argtypes = [vp, i]
     L.snl_scene_load_obj.argtypes = [vp, C.c_char_p, C.c_char_p, C.c_char_p, i, i]
     L.snl_scene_counts.argtypes = [vp, ip, ip, ip, ip, ip]
     L.snl_scene_copy_host_bvh.argtypes = [vp, vp, vp, vp, vp]
@@ -361,6 +362,10 @@ class Scene:
         for k, v in (gvals.items() if isinstance(gvals, dict) else enumerate(gvals)):
             g[k] = v
         self._check(self.L.snl_set_options(self.h, _ptr(g)))
+
+    def set_reflection_depth(self, depth: int):
+        """1 = the reference's cap (src/scene_trace.cpp:454), 2 = two bounces (BASELINE config 5; beyond the reference)."""
+        self._check(self.L.snl_set_reflection_depth(self.h, depth))
 
     def load_obj(self, obj_path, mtl_path=None, tex_dir=None, flip_normals=0, build_flags=USE_SAH):
         self._check(self.L.snl_scene_load_obj(self.h, obj_path.encode(), (mtl_path or "").encode(),

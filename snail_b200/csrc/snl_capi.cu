@@ -280,6 +280,7 @@ int snl::make_scene_dev(snl_scene *s, SceneDev &S, const float *shareOrigin, uns
 	S.gvRefl = s->gVals[7];
 	S.gvTint = 0;
 	S.gvSuper = s->gVals[9];
+	S.reflDepth2 = s->reflDepth == 2 && s->gVals[7] && !s->gVals[1];
 	S.hasUber = s->hasUber;
 	S.hasTransp = s->hasTransp;
 	S.counters = s->dCounters.ptr;
@@ -317,6 +318,8 @@ int snl::prepare_frame(snl_scene *s, const snl_camera *cam, int W, int H, int ra
 	if(int r = make_scene_dev(s, S, cam->pos, &sharedLights))
 		return r;
 	SNL_REQUIRE(!(S.instances && S.gvSuper), SNL_ERR_UNSUPPORTED, "gVals[9] supersampling is not available on an instanced scene");
+	SNL_REQUIRE(!(S.reflDepth2 && (S.instances || S.hasTransp || S.gvSuper)), SNL_ERR_UNSUPPORTED,
+				"reflection depth 2 is only available on plain scenes (no instances, no transparent material, no gVals[9])");
 	if(s->gVals[8]) {
 		S.gvTint = 1;
 		memcpy(S.tint, kRankTint[(unsigned)rank % 16], 12);
@@ -776,6 +779,14 @@ int snl_set_options(snl_scene *s, const int gVals[16]) {
 	return SNL_OK;
 }
 
+int snl_set_reflection_depth(snl_scene *s, int depth) {
+	SNL_REQUIRE(s, SNL_ERR_INVALID, "null scene");
+	SNL_REQUIRE(depth == 1 || depth == 2, SNL_ERR_UNSUPPORTED, "reflection depth %d (1 = the reference's cap, 2)", depth);
+	s->reflDepth = depth;
+	s->tune.key = -1;
+	return SNL_OK;
+}
+
 int snl_scene_counts(snl_scene *s, int *nNodes, int *nTris, int *nMatIds, int *depth, int *nMaterials) {
 	SNL_REQUIRE(s, SNL_ERR_INVALID, "null scene");
 	if(nNodes)
@@ -1014,7 +1025,7 @@ static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, cons
 		packets = s->dPackets.ptr;
 	}
 	const int nPk = packets ? s->nPackets : ((W + 15) / 16) * ((H + 15) / 16);
-	if(S.gvRefl && !S.gvDepth && !s->fused && !S.hasTransp && !S.gvSuper && !S.instances && !S.cullMask && nPk > 0) {
+	if(S.gvRefl && !S.gvDepth && !s->fused && !S.reflDepth2 && !S.hasTransp && !S.gvSuper && !S.instances && !S.cullMask && nPk > 0) {
 		// reflection bounce: wavefront pipeline with queue-driven persistent traversal of the incoherent rays
 		const size_t NL = (size_t)nPk * kPacket, nl = std::max<size_t>(S.nLights, 1);
 		SNL_REQUIRE(NL * nl < 0xffffffffull, SNL_ERR_UNSUPPORTED, "frame too large for 32-bit ray ids");
@@ -1062,7 +1073,7 @@ static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, cons
 		const char *pin = getenv("SNL_RENDER_VARIANT");
 		if(pin && (pin[0] == '0' || pin[0] == '1'))
 			T.choice = pin[0] - '0';
-		else if(S.hasTransp || S.gvSuper || S.instances || nPk < 4 * s->smCount)
+		else if(S.hasTransp || S.gvSuper || S.instances || S.reflDepth2 || nPk < 4 * s->smCount)
 			T.choice = 0;  // only the plain kernel has the second variant; tiny frames are not worth tuning
 	}
 	if(T.choice < 0) {

@@ -973,16 +973,17 @@ __device__ __forceinline__ float box_point_distance_sq(const float lo[3], const 
 // their own where the attenuation is 0 (trace_light), shadow rays of cullable lights are counted per (level, light)
 // in shared memory, every warp leaves its level boxes there, and cull_resolve() at the end of the kernel keeps the
 // counts of the (level, light) pairs the reference would have traced. cull_state_init() + barrier at kernel start.
+enum { kCullLevels = 3 };  // primary rays, first bounce, second bounce (FLAGS bit 8)
 struct CullState {
-	float box[2][kPacket / 32][6];
-	unsigned cnt[2][kMaxLights];
+	float box[kCullLevels][kPacket / 32][6];
+	unsigned cnt[kCullLevels][kMaxLights];
 };
 __device__ __forceinline__ CullState &cull_state() {
 	__shared__ CullState c;
 	return c;
 }
 __device__ __forceinline__ void cull_state_init() {
-	if(threadIdx.x < 2 * kMaxLights)
+	if(threadIdx.x < kCullLevels * kMaxLights)
 		(&cull_state().cnt[0][0])[threadIdx.x] = 0;
 }
 __device__ __forceinline__ void cull_box_store(int level, bool sel, float px, float py, float pz) {
@@ -1000,7 +1001,7 @@ __device__ __forceinline__ void cull_box_store(int level, bool sel, float px, fl
 }
 __device__ __forceinline__ void cull_resolve(const SceneDev &S, PacketCounts &pc) {
 	__syncthreads();
-	if((int)threadIdx.x >= 2 * S.nLights)
+	if((int)threadIdx.x >= kCullLevels * S.nLights)
 		return;
 	const int level = (int)threadIdx.x / S.nLights, li = (int)threadIdx.x % S.nLights;
 	const CullState &c = cull_state();
@@ -1058,8 +1059,11 @@ template <int LEVEL, bool SHARED, int FLAGS, bool DEPTH0>
 __device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet originPre, bool active, int maskGen,
 											   float ox, float oy, float oz, float dx, float dy, float dz, LevelOut &f,
 											   float &hitDist, bool &depthOnly, PacketCounts &pc, TravCount &tc) {
-	// FLAGS: 1 = the scene can start transparency passes, 2 = instanced scene (DBVH)
+	// FLAGS: 1 = the scene can start transparency passes, 2 = instanced scene (DBVH), 4 = deferred light-cull accounting,
+	// 8 = TWO reflection bounces (snl_set_reflection_depth(2): the reference's own cap is `cache.reflections < 1`,
+	// src/scene_trace.cpp:454; BASELINE config 5 asks for depth 2, which is that condition relaxed to `< 2`)
 	constexpr bool TRANSP = (FLAGS & 1) != 0, INST = (FLAGS & 2) != 0;
+	constexpr int MAXREFL = (FLAGS & 8) ? 2 : 1;
 	Hit h;
 	h.dist = CUDART_INF_F;
 	h.obj = 0;
@@ -1109,19 +1113,21 @@ __device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet o
 			boxSlot = packet_box_post(sel, s.px, s.py, s.pz, pc);
 	}
 
-	if(LEVEL == 0 && S.gvRefl) {  // src/scene_trace.cpp:454-466, TraceReflection :603-618
+	if constexpr(LEVEL < MAXREFL) {
+	if(S.gvRefl) {  // src/scene_trace.cpp:454-466, TraceReflection :603-618
 		// selector.All() of the packet (src/scene_trace.cpp:615-617) picks RayGroup<0,0> or <0,1> for the bounce; only
 		// UberMaterial::Shade_ looks at it, so the vote is skipped for scenes without one
 		const int refMask = S.hasUber ? packet_vote_post(sel, pc) : 0;
 		float rx, ry, rz, rox, roy, roz;
 		reflection_ray(s, dx, dy, dz, rx, ry, rz, rox, roy, roz);
 		float cr = 0.0f, cg = 0.0f, cb = 0.0f;
-		raytrace_lane<1, false, FLAGS>(S, PreSet{nullptr, nullptr}, sel, refMask, rox, roy, roz, rx, ry, rz, cr, cg, cb, pc, tc);
+		raytrace_lane<LEVEL + 1, false, FLAGS>(S, PreSet{nullptr, nullptr}, sel, refMask, rox, roy, roz, rx, ry, rz, cr, cg, cb, pc, tc);
 		if(sel) {
 			s.dr = s.dr + (cr - s.dr) * 0.3f;
 			s.dg = s.dg + (cg - s.dg) * 0.3f;
 			s.db = s.db + (cb - s.db) * 0.3f;
 		}
+	}
 	}
 	f.ar = s.dr;
 	f.ag = s.dg;

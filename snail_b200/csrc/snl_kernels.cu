@@ -187,7 +187,8 @@ __device__ __forceinline__ unsigned conv_channel(float c) {
 #ifndef SNL_RENDER_MIN_BLOCKS
 #define SNL_RENDER_MIN_BLOCKS 4
 #endif
-// FLAGS: 1 = the scene has a material that can start a transparency pass, 2 = instanced scene (DBVH). SUPER: gVals[9], every 16x16 output packet is
+// FLAGS: 1 = the scene has a material that can start a transparency pass, 2 = instanced scene (DBVH), 8 = two reflection
+// bounces (plain scenes only). SUPER: gVals[9], every 16x16 output packet is
 // traced as four 16x16 packets of the 2W x 2H image and box-filtered (src/render.cpp:71-110).
 // MINB: resident CTAs per SM the register allocation aims for. 4 (64 registers) suits scenes whose hot set sits in L1;
 // 5 (48 registers, a few more spills) hides more latency on large scenes: +1.9 % on sponza_like, -2 % on feline.
@@ -200,8 +201,9 @@ __device__ __forceinline__ void render_packet(const SceneDev &S, const PreSet &p
 											  PacketCounts &pc, TravCount &tc) {
 	const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
 	// the plain kernel settles the per-packet light cull's ray accounting at its end instead of with barriers per level
-	constexpr int LFLAGS = (FLAGS == 0 && !SUPER) ? 4 : FLAGS;
-	if(LFLAGS == 4 && S.cullMask) {
+	constexpr int LFLAGS = ((FLAGS & ~8) == 0 && !SUPER) ? (4 | FLAGS) : FLAGS;
+	constexpr bool DEFER = (LFLAGS & 4) != 0;
+	if(DEFER && S.cullMask) {
 		cull_state_init();
 		__syncthreads();
 	}
@@ -254,7 +256,7 @@ __device__ __forceinline__ void render_packet(const SceneDev &S, const PreSet &p
 		}
 		__syncwarp();
 	}
-	if(LFLAGS == 4 && S.cullMask)
+	if(DEFER && S.cullMask)
 		cull_resolve(S, pc);
 }
 
@@ -432,6 +434,8 @@ cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenPara
 			SNL_LAUNCH_RENDER(2, false, MB, true);
 		else if(S.hasTransp)
 			SNL_LAUNCH_RENDER(1, false, MB, true);
+		else if(S.reflDepth2)
+			SNL_LAUNCH_RENDER(8, false, MB, true);
 		else if(variant == 1)
 			SNL_LAUNCH_RENDER(0, false, MB + 1, true);
 		else
@@ -447,6 +451,8 @@ cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenPara
 	}
 	else if(S.gvSuper)
 		SNL_LAUNCH_RENDER(0, true, MB, false);
+	else if(S.reflDepth2)
+		SNL_LAUNCH_RENDER(8, false, MB, false);
 	else if(variant == 1)
 		SNL_LAUNCH_RENDER(0, false, MB + 1, false);
 	else
@@ -457,7 +463,7 @@ cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenPara
 
 int render_ctas_per_sm(const SceneDev &S, int variant) {
 	const int MB = SNL_RENDER_MIN_BLOCKS;
-	return (!S.instances && !S.hasTransp && !S.gvSuper && variant == 1) ? MB + 1 : MB;
+	return (!S.instances && !S.hasTransp && !S.gvSuper && !S.reflDepth2 && variant == 1) ? MB + 1 : MB;
 }
 
 // ---- multi-GPU frame protocol (CommCtl in rank 0's memory, see snl_comm.cu) ------------------------------------

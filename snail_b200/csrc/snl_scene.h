@@ -105,6 +105,7 @@ struct snl_scene {
 	snl::PreCacheEntry originPre;  // camera / shared ray origin of the last call
 
 	int gVals[16] = {0};
+	int reflDepth = 1;  // bounces followed when gVals[7] is on: 1 = the reference's cap, 2 = snl_set_reflection_depth(2)
 
 	snl::DevBuf<snl::Counters> dCounters;
 	snl::DevBuf<unsigned char> dImage;  // staging image for snl_render (host output)

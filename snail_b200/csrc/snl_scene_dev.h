@@ -30,6 +30,7 @@ struct SceneDev {
 	int gvDepth, gvFull, gvRefl, gvTint;  // gVals[1], [6], [7], [8]
 	int gvSuper;                          // gVals[9]: 2x2 supersampling in Render()
 	int hasTransp;                        // a material can start a transparency pass (fTransparency and opacity < 1)
+	int reflDepth2;                       // two reflection bounces (snl_set_reflection_depth(2)) - plain scenes only
 	int hasUber;                          // any UberMaterial in the table (its Shade depends on the packet mask)
 	unsigned cullMask;                    // bit i: light i does not reach the whole scene box, so the per-packet light
 										  // cull of Scene::RayTrace (src/scene_trace.cpp:494-499) can skip it somewhere
