@@ -90,7 +90,10 @@ typedef struct snl_stats {
 	uint64_t node_visits;   /* only counted when the library is built with SNL_COUNTERS */
 	uint64_t tri_tests;     /* idem: 48-byte per-origin triangle records tested */
 	uint64_t gtri_tests;    /* idem: 64-byte general triangle records tested (reflection rays) */
-	float kernel_ms;        /* device time of the last call's kernels (CUDA events on the scene's stream) */
+	uint64_t transparency_truncated; /* rays whose chain of transparent surfaces was cut after 8 (the reference's
+	                                    recursion is unbounded); 0 = the frame is exactly the reference's */
+	float kernel_ms;        /* device time of the last call (CUDA events on the scene's stream): its kernels; for snl_render
+	                           with a host image also the row-band device->host copies queued behind them */
 } snl_stats;
 
 const char *snl_last_error(void);
@@ -127,7 +130,8 @@ float snl_scene_build_ms(snl_scene *);
  * from then on snl_render* and snl_trace_primary_inst walk top tree -> instance -> BVH on the device. Like the
  * reference's Scene<DBVH> (HasShadingData() == 0) an instanced scene is shaded with the simple path: geometric normal
  * rotated into world space, default material; shadows and the reflection bounce work. n = 0 returns to the plain BVH.
- * snl_trace_rays / snl_trace_shadow / snl_raytrace and gVals[9] return SNL_ERR_UNSUPPORTED while instanced. */
+ * snl_trace_rays / snl_trace_shadow / snl_raytrace and gVals[9] return SNL_ERR_UNSUPPORTED while instanced. New geometry
+ * (snl_scene_set_geometry / snl_scene_build_device / snl_scene_load_obj) drops the instances: set them again after it. */
 typedef struct snl_instance {
 	float rotation[9]; /* rotation[0..2].xyz */
 	float translation[3];

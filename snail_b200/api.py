@@ -92,7 +92,7 @@ class Texture(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("rays", C.c_uint64), ("primary", C.c_uint64), ("shadow", C.c_uint64), ("reflection", C.c_uint64),
                 ("reflection_shadow", C.c_uint64), ("transparency", C.c_uint64), ("node_visits", C.c_uint64), ("tri_tests", C.c_uint64), ("gtri_tests", C.c_uint64),
-                ("kernel_ms", C.c_float)]
+                ("transparency_truncated", C.c_uint64), ("kernel_ms", C.c_float)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

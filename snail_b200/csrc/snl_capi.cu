@@ -51,10 +51,11 @@ enum { kTopStackHost = 66 };  // = kTopStack of snl_device.cuh (DBVH::maxDepth +
 struct Flattener {
 	const std::vector<RefNode> &ref;
 	std::vector<GpuNode> out;
+	std::vector<unsigned char> seen;  // a well-formed tree reaches every node once: a second visit is a cycle / shared child
 	int maxDepth = 0;
 	bool bad = false;
 
-	explicit Flattener(const std::vector<RefNode> &r) : ref(r) {}
+	explicit Flattener(const std::vector<RefNode> &r) : ref(r), seen(r.size(), 0) {}
 
 	static int leaf_link(int first, int count) { return ~(first | ((count - 1) << kLeafFirstBits)); }
 
@@ -80,10 +81,11 @@ struct Flattener {
 	// link for reference node r; leaves holding more than kLeafMaxCount triangles become a chain of inner nodes
 	// that repeat the leaf's box (same set of triangles tested, same result).
 	int link_for(int r, int depth) {
-		if(r < 0 || r >= (int)ref.size() || depth > 4096) {
+		if(bad || r < 0 || r >= (int)ref.size() || depth > 1024 || seen[r]) {
 			bad = true;
 			return leaf_link(0, 1);
 		}
+		seen[r] = 1;
 		const RefNode &n = ref[r];
 		if(n.sub & 0x80000000) {
 			int first = n.sub & 0x7fffffff, count = n.count;
@@ -158,6 +160,7 @@ int sync_and_stats(snl_scene *s, snl_stats *stats) {
 		stats->reflection = c.reflection;
 		stats->reflection_shadow = c.reflection_shadow;
 		stats->transparency = c.transparency;
+		stats->transparency_truncated = c.transp_truncated;
 		stats->rays = c.primary + c.shadow + c.reflection + c.reflection_shadow + c.transparency;
 		stats->node_visits = c.node_visits;
 		stats->tri_tests = c.tri_tests;
@@ -204,9 +207,7 @@ int snl::ensure_pre(snl_scene *s, PreCacheEntry &e, const float origin[3]) {
 	if(e.valid && memcmp(e.origin, origin, 12) == 0)
 		return SNL_OK;
 	SNL_CUDA(e.buf.reserve((size_t)s->nTris));
-	SNL_CUDA(e.nodes.reserve((size_t)s->nGpuNodes));
-	SNL_CUDA(launch_pretransform(s->dTris.ptr, s->nTris, s->dNodes.ptr, s->nGpuNodes, origin, e.buf.ptr, e.nodes.ptr,
-								 s->stream));
+	SNL_CUDA(launch_pretransform(s->dTris.ptr, s->nTris, origin, e.buf.ptr, s->stream));
 	s->launches++;
 	memcpy(e.origin, origin, 12);
 	e.valid = true;
@@ -399,12 +400,12 @@ void snl_scene_destroy(snl_scene *s) {
 	s->dTexs.release();
 	for(auto &t : s->dTexData)
 		t.release();
-	for(auto &e : s->lightPre) {
+	for(auto &e : s->lightPre)
 		e.buf.release();
-		e.nodes.release();
-	}
 	s->originPre.buf.release();
-	s->originPre.nodes.release();
+	s->dFarmTiles.release();
+	s->dFarmOffsets.release();
+	s->dFarm.release();
 	s->dCounters.release();
 	s->dImage.release();
 	for(auto &b : s->dScratch)
@@ -505,6 +506,11 @@ static int build_geometry_on_device(snl_scene *s) {
 
 static int upload_geometry(snl_scene *s) {
 	const HostBVH &h = s->host;
+	// instance boxes and the top-level tree were built from the OLD tree's box: a new tree starts as a plain BVH again
+	// (call snl_scene_set_instances after the geometry)
+	s->instances.clear();
+	s->topNodes.clear();
+	s->tune.key = -1;
 	if(h.nodes.empty() && !h.tris.empty())
 		return build_geometry_on_device(s);
 	s->devBuilt = false;
@@ -699,7 +705,8 @@ static int upload_materials(snl_scene *s, const snl_material *mats, int nMats, c
 	}
 	for(auto &t : s->dTexData)
 		t.release();
-	s->dTexData.assign(nTex, DevBuf<unsigned char>());
+	s->dTexData.clear();
+	s->dTexData.resize(nTex);
 	std::vector<DevTexture> dt(nTex);
 	for(int i = 0; i < nTex; i++) {
 		const snl_texture &t = tex[i];

@@ -76,7 +76,7 @@ struct snl_comm {
 	int nBands = 1, rowsPerBand = 1;
 	cudaStream_t copyStream[kCommBands] = {};
 	cudaEvent_t copyEv[kCommBands] = {}, openEv = nullptr;
-	unsigned long long *hStats = nullptr;  // pinned: 8 counters + error word
+	unsigned long long *hStats = nullptr;  // pinned: kCounters counters + error word
 	float lastMs = 0.0f;
 };
 
@@ -385,8 +385,8 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 			// every rank has published = every packet of the frame is stored and every counter is in
 			SNL_CUDA(launch_wait_counter(&ctl->statsArrived[slot], (unsigned)c->world, &ctl->error, s->stream));
 			s->launches++;
-			SNL_CUDA(cudaMemcpyAsync(c->hStats, ctl->stats[slot], 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s->stream));
-			SNL_CUDA(cudaMemcpyAsync(c->hStats + 8, &ctl->error, sizeof(unsigned), cudaMemcpyDeviceToHost, s->stream));
+			SNL_CUDA(cudaMemcpyAsync(c->hStats, ctl->stats[slot], sizeof(Counters), cudaMemcpyDeviceToHost, s->stream));
+			SNL_CUDA(cudaMemcpyAsync(c->hStats + kCounters, &ctl->error, sizeof(unsigned), cudaMemcpyDeviceToHost, s->stream));
 		}
 	}
 	c->seq++;
@@ -400,7 +400,7 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 	}
 	c->lastMs = ms;
 	if(isRoot)
-		SNL_REQUIRE(*(const unsigned *)(c->hStats + 8) == 0, SNL_ERR_STATE,
+		SNL_REQUIRE(*(const unsigned *)(c->hStats + kCounters) == 0, SNL_ERR_STATE,
 					"snl_render_multi: a rank did not arrive within the time-out (every rank must call it once per frame)");
 	if(stats) {
 		memset(stats, 0, sizeof(*stats));
@@ -416,6 +416,7 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 		stats->reflection = k.reflection;
 		stats->reflection_shadow = k.reflection_shadow;
 		stats->transparency = k.transparency;
+		stats->transparency_truncated = k.transp_truncated;
 		stats->rays = k.primary + k.shadow + k.reflection + k.reflection_shadow + k.transparency;
 		stats->node_visits = k.node_visits;
 		stats->tri_tests = k.tri_tests;

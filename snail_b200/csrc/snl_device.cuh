@@ -22,14 +22,9 @@ __device__ __forceinline__ int4 ldg4(const Int4 *p) { return __ldg(reinterpret_c
 // L1 one wavefront per distinct line and load instruction, so a 64-byte record costs two of these instead of four
 // 128-bit loads.
 __device__ __forceinline__ void ldg8(const void *p, float4 &lo, float4 &hi) {
-#ifndef SNL_NO_LDG256
 	asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
 				 : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w)
 				 : "l"(p));
-#else
-	lo = __ldg(reinterpret_cast<const float4 *>(p));
-	hi = __ldg(reinterpret_cast<const float4 *>(p) + 1);
-#endif
 }
 
 #ifdef SNL_COUNTERS
@@ -49,7 +44,6 @@ struct TravCount {
 // v, come from the triangle test alone and stay bit-identical (tests/test_gpu_golden.py).
 __device__ __forceinline__ bool box_test(float minx, float maxx, float miny, float maxy, float minz, float maxz, float oix,
 										 float oiy, float oiz, float ix, float iy, float iz, float dist, float &lminOut) {
-#ifndef SNL_BOX_EXACT
 	float l1 = fmaf(minx, ix, -oix), l2 = fmaf(maxx, ix, -oix);
 	float lmin = fminf(l1, l2), lmax = fmaxf(l1, l2);
 	l1 = fmaf(miny, iy, -oiy);
@@ -58,33 +52,6 @@ __device__ __forceinline__ bool box_test(float minx, float maxx, float miny, flo
 	lmax = fminf(lmax, fmaxf(l1, l2));
 	l1 = fmaf(minz, iz, -oiz);
 	l2 = fmaf(maxz, iz, -oiz);
-#else  // oi* = the origin itself: the reference's expression
-	float l1 = ix * (minx - oix), l2 = ix * (maxx - oix);
-	float lmin = fminf(l1, l2), lmax = fmaxf(l1, l2);
-	l1 = iy * (miny - oiy);
-	l2 = iy * (maxy - oiy);
-	lmin = fmaxf(lmin, fminf(l1, l2));
-	lmax = fminf(lmax, fmaxf(l1, l2));
-	l1 = iz * (minz - oiz);
-	l2 = iz * (maxz - oiz);
-#endif
-	lmin = fmaxf(lmin, fminf(l1, l2));
-	lmax = fminf(lmax, fmaxf(l1, l2));
-	lminOut = lmin;
-	return lmax >= 0.0f && lmin <= fminf(lmax, dist);
-}
-
-// The same test on a box already translated by the ray origin (minx = box.min.x - origin.x, ...).
-__device__ __forceinline__ bool box_test_rel(float minx, float maxx, float miny, float maxy, float minz, float maxz, float ix,
-											 float iy, float iz, float dist, float &lminOut) {
-	float l1 = ix * minx, l2 = ix * maxx;
-	float lmin = fminf(l1, l2), lmax = fmaxf(l1, l2);
-	l1 = iy * miny;
-	l2 = iy * maxy;
-	lmin = fmaxf(lmin, fminf(l1, l2));
-	lmax = fminf(lmax, fmaxf(l1, l2));
-	l1 = iz * minz;
-	l2 = iz * maxz;
 	lmin = fmaxf(lmin, fminf(l1, l2));
 	lmax = fminf(lmax, fmaxf(l1, l2));
 	lminOut = lmin;
@@ -160,21 +127,10 @@ __device__ __forceinline__ void tri_nearest_gen(const GenTri *__restrict__ t, in
 // Children are visited nearest first (by slab entry distance instead of the packet's firstNode^sign[axis]); only
 // exact-t ties can resolve differently from the reference's packet order.
 //
-// SHARED rays (one origin for the whole launch: camera or light) read node boxes that were translated by the origin
-// once per frame (k_pretransform: the very subtraction `min - origin` the reference performs per packet per node,
-// src/bounding_box.cpp:68-71, so the products are bit-identical) and PreTri records; per-ray-origin rays read the
-// untranslated nodes and GenTri records.
+// SHARED rays (one origin for the whole launch: camera or light) test PreTri records (k_pretransform), per-ray-origin
+// rays GenTri records; both walk the ONE node array with the FMA slab test above.
 
 enum { kSentinel = 0x7fffffff };
-
-// SNL_REL_NODES: shared-origin rays walk a per-origin copy of the nodes with boxes translated by the origin (one FMUL
-// per slab plane). Default off: with the slab test written as one FMA per plane every ray walks the ONE node array,
-// which costs the same instructions and keeps a third of the node bytes in L1 / L2.
-#ifdef SNL_REL_NODES
-constexpr bool kRelNodes = true;
-#else
-constexpr bool kRelNodes = false;
-#endif
 
 // One step of the walk after the two box tests of the node at `cur`: go to the nearer hit child (push the farther), or
 // pop; a leaf reached while none is parked gets parked and the walk continues with the next stack entry. stack[-1]
@@ -212,18 +168,16 @@ constexpr bool kRelNodes = false;
 	} while(0)
 #else
 // Default: plain stack in local memory, [0] = sentinel. Fewer instructions per step than the register-cached top
-// (SNL_STEP_TOS, kept for the wavefront kernels), one more dependent LDL on a double pop: 0.5 % faster on B200.
+// (SNL_STEP_TOS, which the wavefront kernels keep), one more dependent LDL on a double pop: 0.5 % faster on B200.
 #define SNL_STACK_DECL()   \
 	int stack[kStack + 1]; \
 	stack[0] = kSentinel;  \
 	int sp = 1
 #define SNL_POP(dst) dst = stack[--sp]
-#ifndef SNL_STEP_TWOPOP
-#define SNL_STEP_ONEPOP  // +3.8 % sponza_like, +3.4 % feline on B200 against the two-pop step below
-#endif
-#ifdef SNL_STEP_ONEPOP
+#define SNL_STEP_ONEPOP
 // One pop site per step: a leaf that gets parked and a step that hit nothing both take the next stack entry. (A popped
 // entry that is itself a leaf ends the inner walk even when nothing is parked yet; the triangle loop takes it from cur.)
+// +3.8 % sponza_like, +3.4 % feline on B200 against a step with two pop sites.
 #define SNL_TRAVERSE_STEP()                                   \
 	do {                                                      \
 		const bool both_ = h0 && h1, any_ = h0 || h1;         \
@@ -240,27 +194,9 @@ constexpr bool kRelNodes = false;
 			next_ = stack[--sp];                              \
 		cur = next_;                                          \
 	} while(0)
-#else
-#define SNL_TRAVERSE_STEP()                                   \
-	do {                                                      \
-		const bool both_ = h0 && h1, any_ = h0 || h1;         \
-		const bool swap_ = lmin1 < lmin0;                     \
-		int next_ = both_ ? (swap_ ? l1 : l0) : (h0 ? l0 : l1); \
-		if(both_)                                             \
-			stack[sp++] = swap_ ? l0 : l1;                    \
-		if(!any_)                                             \
-			next_ = stack[--sp];                              \
-		if(next_ < 0 && leaf == 0) {                          \
-			leaf = next_;                                     \
-			next_ = stack[--sp];                              \
-		}                                                     \
-		cur = next_;                                          \
-	} while(0)
-#endif
 #endif
 
-// Both children of one inner node. REL: boxes are already relative to the ray origin.
-template <bool REL>
+// Both children of one inner node. o* = origin * idir.
 __device__ __forceinline__ void node_test(const GpuNode *__restrict__ n, float ox, float oy, float oz, float ix, float iy,
 										  float iz, float dist, bool &h0, bool &h1, float &lmin0, float &lmin1, int &l0, int &l1) {
 	float4 b0, b1, bz, lk;
@@ -268,14 +204,8 @@ __device__ __forceinline__ void node_test(const GpuNode *__restrict__ n, float o
 	ldg8(&n->bz, bz, lk);
 	l0 = __float_as_int(lk.x);
 	l1 = __float_as_int(lk.y);
-	if(REL) {
-		h0 = box_test_rel(b0.x, b0.y, b0.z, b0.w, bz.x, bz.y, ix, iy, iz, dist, lmin0);
-		h1 = box_test_rel(b1.x, b1.y, b1.z, b1.w, bz.z, bz.w, ix, iy, iz, dist, lmin1);
-	}
-	else {
-		h0 = box_test(b0.x, b0.y, b0.z, b0.w, bz.x, bz.y, ox, oy, oz, ix, iy, iz, dist, lmin0);
-		h1 = box_test(b1.x, b1.y, b1.z, b1.w, bz.z, bz.w, ox, oy, oz, ix, iy, iz, dist, lmin1);
-	}
+	h0 = box_test(b0.x, b0.y, b0.z, b0.w, bz.x, bz.y, ox, oy, oz, ix, iy, iz, dist, lmin0);
+	h1 = box_test(b1.x, b1.y, b1.z, b1.w, bz.z, bz.w, ox, oy, oz, ix, iy, iz, dist, lmin1);
 }
 
 // BVH::TraversePrimaryN per ray (src/bvh/traverse.cpp:14-80).
@@ -283,15 +213,9 @@ template <bool SHARED, bool SHORDER = false>
 __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nodes, const void *__restrict__ tris,
 												 float ox, float oy, float oz, float dx, float dy, float dz, float ix,
 												 float iy, float iz, Hit &h, TravCount &tc) {
-	// default: the top of the stack lives in a register (tos), a pop hands out the next node without waiting for local
-	// memory; stack[-1] is a guard slot because popping the sentinel reads it
 	SNL_STACK_DECL();
 	int cur = 0;
-#ifndef SNL_BOX_EXACT
 	const float bx = ox * ix, by = oy * iy, bz = oz * iz;  // box_test's origin * idir
-#else
-	const float bx = ox, by = oy, bz = oz;
-#endif
 	while(cur != kSentinel) {
 		int leaf = 0;  // parked leaf link (< 0), 0 = none
 		while((unsigned)cur < (unsigned)kSentinel) {
@@ -299,12 +223,10 @@ __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nod
 			bool h0, h1;
 			float lmin0, lmin1;
 			int l0, l1;
-			node_test<SHARED && kRelNodes>(nodes + cur, bx, by, bz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
+			node_test(nodes + cur, bx, by, bz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
 			SNL_TRAVERSE_STEP();
-#ifndef SNL_NO_VOTE
 			if(!__any_sync(__activemask(), leaf == 0))
 				break;
-#endif
 		}
 #ifdef SNL_STEP_ONEPOP
 		if(leaf == 0 && cur < 0) {
@@ -340,11 +262,7 @@ template <bool GEN = false>
 __device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ nodes, const void *__restrict__ tris, float ox,
 												float oy, float oz, float dx, float dy, float dz, float ix, float iy, float iz,
 												float dist, TravCount &tc) {
-#ifndef SNL_BOX_EXACT
 	const float bx = ox * ix, by = oy * iy, bz = oz * iz;  // box_test's origin * idir
-#else
-	const float bx = ox, by = oy, bz = oz;
-#endif
 	SNL_STACK_DECL();
 	int cur = 0;
 	bool occluded = false;
@@ -355,12 +273,10 @@ __device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ node
 			bool h0, h1;
 			float lmin0, lmin1;
 			int l0, l1;
-			node_test<kRelNodes>(nodes + cur, bx, by, bz, ix, iy, iz, dist, h0, h1, lmin0, lmin1, l0, l1);
+			node_test(nodes + cur, bx, by, bz, ix, iy, iz, dist, h0, h1, lmin0, lmin1, l0, l1);
 			SNL_TRAVERSE_STEP();
-#ifndef SNL_NO_VOTE
 			if(!__any_sync(__activemask(), leaf == 0))
 				break;
-#endif
 		}
 #ifdef SNL_STEP_ONEPOP
 		if(leaf == 0 && cur < 0) {
@@ -449,7 +365,7 @@ __device__ __forceinline__ void traverse_nearest_inst(const SceneDev &S, float o
 			bool h0, h1;
 			float lmin0, lmin1;
 			int l0, l1;
-			node_test<false>(S.topNodes + cur, bx, by, bz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
+			node_test(S.topNodes + cur, bx, by, bz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
 			const bool swap = lmin1 < lmin0;
 			if(h0 && h1) {
 				stack[sp++] = swap ? l0 : l1;
@@ -490,7 +406,7 @@ __device__ __forceinline__ bool traverse_shadow_inst(const SceneDev &S, float ox
 			bool h0, h1;
 			float lmin0, lmin1;
 			int l0, l1;
-			node_test<false>(S.topNodes + cur, bx, by, bz, ix, iy, iz, dist, h0, h1, lmin0, lmin1, l0, l1);
+			node_test(S.topNodes + cur, bx, by, bz, ix, iy, iz, dist, h0, h1, lmin0, lmin1, l0, l1);
 			if(h0 && h1) {
 				stack[sp++] = l1;
 				cur = l0;
@@ -829,7 +745,7 @@ __device__ __forceinline__ bool trace_light(const SceneDev &S, int li, bool sel,
 		return true;
 	const bool occluded =
 		INST ? traverse_shadow_inst(S, L.pos[0], L.pos[1], L.pos[2], fx, fy, fz, safe_inv(fx), safe_inv(fy), safe_inv(fz), tmax, tc)
-			 : traverse_shadow(kRelNodes ? S.lightPre[li].nodes : S.nodes, S.lightPre[li].tris, L.pos[0], L.pos[1], L.pos[2], fx,
+			 : traverse_shadow(S.nodes, S.lightPre[li].tris, L.pos[0], L.pos[1], L.pos[2], fx,
 							   fy, fz, safe_inv(fx), safe_inv(fy), safe_inv(fz), tmax, tc);
 	if(!occluded && tmax > 0.0f)
 		light_accumulate(L, dot, atten, ldr, ldg, ldb, lsr, lsg, lsb);
@@ -851,6 +767,7 @@ __device__ __forceinline__ void reflection_ray(const Sample &s, float dx, float 
 
 struct PacketCounts {
 	unsigned primary, shadow, reflection, reflection_shadow, transparency;
+	unsigned truncated;  // transparency chains cut at kMaxTransp
 	int voteGen;  // packet votes taken so far (PacketVote), uniform over the CTA
 	int boxGen;   // packet hit boxes posted so far (PacketBox), uniform over the CTA
 };
@@ -1074,7 +991,7 @@ __device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet o
 		if(INST)
 			traverse_nearest_inst<SHARED>(S, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
 		else if(SHARED)
-			traverse_nearest<true>(kRelNodes ? originPre.nodes : S.nodes, originPre.tris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
+			traverse_nearest<true>(S.nodes, originPre.tris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
 		else
 			traverse_nearest<false>(S.nodes, S.gtris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
 		if(!DEPTH0)
@@ -1121,7 +1038,7 @@ __device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet o
 		float rx, ry, rz, rox, roy, roz;
 		reflection_ray(s, dx, dy, dz, rx, ry, rz, rox, roy, roz);
 		float cr = 0.0f, cg = 0.0f, cb = 0.0f;
-		raytrace_lane<LEVEL + 1, false, FLAGS>(S, PreSet{nullptr, nullptr}, sel, refMask, rox, roy, roz, rx, ry, rz, cr, cg, cb, pc, tc);
+		raytrace_lane<LEVEL + 1, false, FLAGS>(S, PreSet{nullptr}, sel, refMask, rox, roy, roz, rx, ry, rz, cr, cg, cb, pc, tc);
 		if(sel) {
 			s.dr = s.dr + (cr - s.dr) * 0.3f;
 			s.dg = s.dg + (cg - s.dg) * 0.3f;
@@ -1195,7 +1112,10 @@ __device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet or
 		LevelOut behind[kMaxTransp];
 		int depth = 0;
 		for(;;) {
-			cont = cont && depth < kMaxTransp;
+			if(cont && depth >= kMaxTransp) {  // the reference would keep recursing: counted, reported in snl_stats
+				pc.truncated++;
+				cont = false;
+			}
 			// transSel.Any() / transSel.All() of the packet (src/scene_trace.cpp:474, :630-633)
 			const int n = __syncthreads_count(cont);
 			if(n == 0)
@@ -1210,7 +1130,7 @@ __device__ __forceinline__ void raytrace_lane(const SceneDev &S, const PreSet or
 			// every lane takes part (shading blocks are warp-wide); only continued lanes take the new level's result
 			LevelOut nf;
 			float nDist;
-			const bool more = raytrace_level<LEVEL, false, FLAGS, false>(S, PreSet{nullptr, nullptr}, cont, n != kPacket ? -1 : 0, ox,
+			const bool more = raytrace_level<LEVEL, false, FLAGS, false>(S, PreSet{nullptr}, cont, n != kPacket ? -1 : 0, ox,
 																		  oy, oz, dx, dy, dz, nf, nDist, depthOnly, pc, tc);
 			if(cont) {
 				f = nf;
@@ -1266,13 +1186,14 @@ template <bool GE> __device__ __forceinline__ bool wait_sys(const unsigned *p, u
 
 // CTA-level aggregation of the per-lane ray counters into the scene's global counters.
 __device__ __forceinline__ void flush_counts(const SceneDev &S, const PacketCounts &pc, const TravCount &tc) {
-	__shared__ unsigned sh[8];
-	if(threadIdx.x < 8)
+	__shared__ unsigned sh[kCounters];
+	if(threadIdx.x < kCounters)
 		sh[threadIdx.x] = 0;
 	__syncthreads();
-	unsigned v[8] = {pc.primary, pc.shadow, pc.reflection, pc.reflection_shadow, tc.nodes, tc.tris, tc.gtris, pc.transparency};
+	unsigned v[kCounters] = {pc.primary, pc.shadow, pc.reflection, pc.reflection_shadow, tc.nodes, tc.tris, tc.gtris, pc.transparency,
+							 pc.truncated};
 #pragma unroll
-	for(int i = 0; i < 8; i++) {
+	for(int i = 0; i < kCounters; i++) {
 		unsigned x = v[i];
 #pragma unroll
 		for(int o = 16; o; o >>= 1)
@@ -1281,7 +1202,7 @@ __device__ __forceinline__ void flush_counts(const SceneDev &S, const PacketCoun
 			atomicAdd(&sh[i], x);
 	}
 	__syncthreads();
-	if(threadIdx.x < 8 && sh[threadIdx.x])
+	if(threadIdx.x < kCounters && sh[threadIdx.x])
 		atomicAdd(reinterpret_cast<unsigned long long *>(S.counters) + threadIdx.x, (unsigned long long)sh[threadIdx.x]);
 }
 

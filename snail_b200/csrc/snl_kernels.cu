@@ -7,21 +7,10 @@
 namespace snl {
 
 // Per-origin records, one launch per origin and frame: Triangle::Collide's sharedOrigin precomputation
-// (src/triangle.cpp:9-18) for every triangle, and every node's child boxes translated by the origin (the
-// `min - origin` / `max - origin` of BBox::Test, src/bounding_box.cpp:68-71, hoisted out of the traversal loop).
-__global__ void __launch_bounds__(256) k_pretransform(const GenTri *__restrict__ gtris, int nTris,
-													 const GpuNode *__restrict__ nodes, int nNodes, float ox, float oy,
-													 float oz, PreTri *__restrict__ out, GpuNode *__restrict__ outNodes) {
+// (src/triangle.cpp:9-18) for every triangle, hoisted from per packet to per frame.
+__global__ void __launch_bounds__(256) k_pretransform(const GenTri *__restrict__ gtris, int nTris, float ox, float oy, float oz,
+													 PreTri *__restrict__ out) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
-	if(outNodes && i < nNodes) {  // only with SNL_REL_NODES (snl_device.cuh)
-		const float4 b0 = ldg4(&nodes[i].b0), b1 = ldg4(&nodes[i].b1), bz = ldg4(&nodes[i].bz);
-		const int4 link = ldg4(&nodes[i].link);
-		float4 *o = reinterpret_cast<float4 *>(outNodes + i);
-		o[0] = make_float4(b0.x - ox, b0.y - ox, b0.z - oy, b0.w - oy);
-		o[1] = make_float4(b1.x - ox, b1.y - ox, b1.z - oy, b1.w - oy);
-		o[2] = make_float4(bz.x - oz, bz.y - oz, bz.z - oz, bz.w - oz);
-		reinterpret_cast<int4 *>(outNodes + i)[3] = link;
-	}
 	if(i >= nTris)
 		return;
 	const float4 ta = ldg4(&gtris[i].a), tba = ldg4(&gtris[i].ba), tca = ldg4(&gtris[i].ca), tn = ldg4(&gtris[i].n);
@@ -54,7 +43,7 @@ __global__ void __launch_bounds__(kPacket) k_primary(SceneDev S, const PreSet pr
 	const int px0 = (blockIdx.x % packetsX) * 16, py0 = (blockIdx.x / packetsX) * 16;
 	const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
 	const int x = px0 + tx, y = py0 + ty;
-	PacketCounts pc = {0, 0, 0, 0, 0};
+	PacketCounts pc = {};
 	TravCount tc = {0, 0, 0};
 	const bool inside = x < W && y < H;
 	if(inside) {
@@ -69,7 +58,7 @@ __global__ void __launch_bounds__(kPacket) k_primary(SceneDev S, const PreSet pr
 			traverse_nearest_inst<true>(S, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, safe_inv(dx), safe_inv(dy),
 										safe_inv(dz), h, tc);
 		else
-			traverse_nearest<true>(kRelNodes ? pre.nodes : S.nodes, pre.tris, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz,
+			traverse_nearest<true>(S.nodes, pre.tris, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz,
 								   safe_inv(dx), safe_inv(dy), safe_inv(dz), h, tc);
 		pc.primary = 1;
 		const size_t o = (size_t)y * W + x;
@@ -96,7 +85,7 @@ __global__ void __launch_bounds__(kPacket) k_trace_rays(SceneDev S, const PreSet
 													 int n, int *__restrict__ triId, float *__restrict__ t,
 													 float *__restrict__ bary) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
-	PacketCounts pc = {0, 0, 0, 0, 0};
+	PacketCounts pc = {};
 	TravCount tc = {0, 0, 0};
 	if(i < n) {
 		const bool active = !mask || mask[i];
@@ -108,7 +97,7 @@ __global__ void __launch_bounds__(kPacket) k_trace_rays(SceneDev S, const PreSet
 			const float *o = SHARED ? o3 : o3 + (size_t)i * 3;
 			const float ox = o[0], oy = o[1], oz = o[2];
 			const float dx = d3[(size_t)i * 3 + 0], dy = d3[(size_t)i * 3 + 1], dz = d3[(size_t)i * 3 + 2];
-			traverse_nearest<SHARED>(SHARED && kRelNodes ? pre.nodes : S.nodes, SHARED ? (const void *)pre.tris : (const void *)S.gtris, ox, oy, oz, dx, dy, dz,
+			traverse_nearest<SHARED>(S.nodes, SHARED ? (const void *)pre.tris : (const void *)S.gtris, ox, oy, oz, dx, dy, dz,
 									 safe_inv(dx), safe_inv(dy), safe_inv(dz), h, tc);
 			pc.primary = 1;
 		}
@@ -130,13 +119,13 @@ __global__ void __launch_bounds__(kPacket) k_trace_rays(SceneDev S, const PreSet
 __global__ void __launch_bounds__(kPacket) k_trace_shadow(SceneDev S, const PreSet pre, float ox, float oy, float oz,
 													   const float *__restrict__ d3, float *__restrict__ tmax, int n) {
 	const int i = blockIdx.x * blockDim.x + threadIdx.x;
-	PacketCounts pc = {0, 0, 0, 0, 0};
+	PacketCounts pc = {};
 	TravCount tc = {0, 0, 0};
 	if(i < n) {
 		const float dist = tmax[i];
 		if(dist >= 0.0f) {
 			const float dx = d3[(size_t)i * 3 + 0], dy = d3[(size_t)i * 3 + 1], dz = d3[(size_t)i * 3 + 2];
-			if(traverse_shadow(kRelNodes ? pre.nodes : S.nodes, pre.tris, ox, oy, oz, dx, dy, dz, safe_inv(dx), safe_inv(dy),
+			if(traverse_shadow(S.nodes, pre.tris, ox, oy, oz, dx, dy, dz, safe_inv(dx), safe_inv(dy),
 							   safe_inv(dz), dist, tc))
 				tmax[i] = -CUDART_INF_F;
 			pc.shadow = 1;
@@ -161,7 +150,7 @@ __global__ void __launch_bounds__(kPacket) k_raytrace(SceneDev S, const PreSet p
 	const float dx = d3[(size_t)src * 3 + 0], dy = d3[(size_t)src * 3 + 1], dz = d3[(size_t)src * 3 + 2];
 	const bool all = __syncthreads_and(active);
 	packet_vote_init();
-	PacketCounts pc = {0, 0, 0, 0, 0};
+	PacketCounts pc = {};
 	TravCount tc = {0, 0, 0};
 	float r = 0.0f, g = 0.0f, b = 0.0f;
 	raytrace_lane<0, SHARED, TRANSP>(S, pre, active, (!SHARED && !all) ? -1 : 0, ox, oy, oz, dx, dy, dz, r, g, b, pc, tc);
@@ -284,7 +273,7 @@ template <int FLAGS, bool SUPER, int MINB, bool DYN>
 __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreSet pre, RayGenParams g, int W, int H,
 												 int packetsX, const int4 *__restrict__ packets,
 												 unsigned char *__restrict__ out, size_t pitch, int firstPacket, const DynCtl ctl) {
-	PacketCounts pc = {0, 0, 0, 0, 0};
+	PacketCounts pc = {};
 	TravCount tc = {0, 0, 0};
 	__shared__ __align__(16) unsigned char tile[SUPER ? 16 : 16 * 48];
 	if(S.hasUber)
@@ -349,16 +338,10 @@ __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreS
 
 static inline unsigned blocks_for(int n, int per) { return (unsigned)((n + per - 1) / per); }
 
-cudaError_t launch_pretransform(const GenTri *gtris, int nTris, const GpuNode *nodes, int nNodes, const float origin[3],
-								PreTri *out, GpuNode *outNodes, cudaStream_t st) {
+cudaError_t launch_pretransform(const GenTri *gtris, int nTris, const float origin[3], PreTri *out, cudaStream_t st) {
 	if(nTris <= 0)
 		return cudaSuccess;
-	if(!kRelNodes) {
-		outNodes = nullptr;
-		nNodes = 0;
-	}
-	k_pretransform<<<blocks_for(nTris > nNodes ? nTris : nNodes, 256), 256, 0, st>>>(gtris, nTris, nodes, nNodes, origin[0],
-																					 origin[1], origin[2], out, outNodes);
+	k_pretransform<<<blocks_for(nTris, 256), 256, 0, st>>>(gtris, nTris, origin[0], origin[1], origin[2], out);
 	return cudaGetLastError();
 }
 
@@ -477,7 +460,7 @@ __global__ void k_frame_open(CommCtl *ctl, unsigned seq, int world) {
 		ctl->cursor[slot] = 0ull;
 		ctl->statsArrived[slot] = 0u;
 	}
-	if(threadIdx.x < 8)
+	if(threadIdx.x < kCounters)
 		ctl->stats[slot][threadIdx.x] = 0ull;
 	if(threadIdx.x < kCommBands)
 		ctl->bandDone[slot][threadIdx.x] = 0u;
@@ -490,7 +473,7 @@ __global__ void k_frame_open(CommCtl *ctl, unsigned seq, int world) {
 
 __global__ void k_frame_publish(CommCtl *ctl, const Counters *local, unsigned seq, int rank) {
 	const unsigned slot = seq & 1u;
-	if(threadIdx.x < 8) {
+	if(threadIdx.x < kCounters) {
 		const unsigned long long v = reinterpret_cast<const unsigned long long *>(local)[threadIdx.x];
 		if(v)
 			atomicAdd_system(&ctl->stats[slot][threadIdx.x], v);

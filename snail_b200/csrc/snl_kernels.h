@@ -13,8 +13,7 @@ struct WfBuffers;
 struct DynCtl;
 struct CommCtl;
 
-cudaError_t launch_pretransform(const GenTri *gtris, int nTris, const GpuNode *nodes, int nNodes, const float origin[3],
-								PreTri *out, GpuNode *outNodes, cudaStream_t st);
+cudaError_t launch_pretransform(const GenTri *gtris, int nTris, const float origin[3], PreTri *out, cudaStream_t st);
 cudaError_t launch_primary(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, int *triId, float *t,
 						   float *bary, int *instId, cudaStream_t st);
 cudaError_t launch_trace_rays(const SceneDev &S, const PreSet &pre, const float *o3, const float *d3,

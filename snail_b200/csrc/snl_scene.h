@@ -19,6 +19,11 @@ void set_error(const char *fmt, ...);
 template <class T> struct DevBuf {
 	T *ptr = nullptr;
 	size_t cap = 0;
+	DevBuf() = default;
+	DevBuf(const DevBuf &) = delete;
+	DevBuf &operator=(const DevBuf &) = delete;
+	DevBuf(DevBuf &&o) noexcept : ptr(o.ptr), cap(o.cap) { o.ptr = nullptr, o.cap = 0; }
+	~DevBuf() { release(); }  // the owner makes its device current first (snl_scene_destroy)
 	cudaError_t reserve(size_t n) {
 		if(n <= cap)
 			return cudaSuccess;
@@ -43,8 +48,7 @@ struct PreCacheEntry {
 	float origin[3];
 	bool valid = false;
 	DevBuf<PreTri> buf;
-	DevBuf<GpuNode> nodes;
-	PreSet set() const { return PreSet{buf.ptr, nodes.ptr}; }
+	PreSet set() const { return PreSet{buf.ptr}; }
 };
 
 }  // namespace snl

@@ -8,10 +8,9 @@ namespace snl {
 enum { kStack = 96, kPacket = 256 };
 
 // Per-origin data (camera or one light), rebuilt by k_pretransform when the origin moves: triangle records with
-// Triangle::Collide's sharedOrigin precomputation applied, and node boxes translated by the origin.
+// Triangle::Collide's sharedOrigin precomputation applied.
 struct PreSet {
 	const PreTri *tris;
-	const GpuNode *nodes;
 };
 
 struct SceneDev {
@@ -43,7 +42,7 @@ struct SceneDev {
 enum { kCommBands = 8, kCommRanks = 16, kCommCtlBytes = 4096 };
 struct CommCtl {
 	unsigned long long cursor[2];               // next packet batch of the frame in this slot
-	unsigned long long stats[2][8];             // Counters of the frame summed over the ranks
+	unsigned long long stats[2][kCounters];            // Counters of the frame summed over the ranks
 	unsigned bandDone[2][kCommBands];           // packets completed per row band
 	unsigned ready[2];                          // seq + 1 once the slot has been opened for frame seq
 	unsigned statsArrived[2];

@@ -122,6 +122,9 @@ struct RayGenParams {
 
 struct Counters {
 	unsigned long long primary, shadow, reflection, reflection_shadow, node_visits, tri_tests, gtri_tests, transparency;
+	unsigned long long transp_truncated;  // rays whose transparency chain was cut at kMaxTransp surfaces
 };
+enum { kCounters = 9 };
+static_assert(sizeof(Counters) == kCounters * 8, "Counters is kCounters u64");
 
 }  // namespace snl

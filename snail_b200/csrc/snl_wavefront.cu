@@ -76,14 +76,14 @@ __global__ void __launch_bounds__(kPacket) k_wf_primary(SceneDev S, const PreSet
 	const unsigned id = blockIdx.x * kPacket + threadIdx.x;
 	float dx, dy, dz;
 	gen_primary(g, px0, py0, tx, ty, dx, dy, dz);
-	PacketCounts pc = {0, 0, 0, 0, 0};
+	PacketCounts pc = {};
 	TravCount tc = {0, 0, 0};
 
 	Hit h;
 	h.dist = CUDART_INF_F;
 	h.obj = 0;
 	h.bu = h.bv = 0.0f;
-	traverse_nearest<true>(kRelNodes ? pre.nodes : S.nodes, pre.tris, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, safe_inv(dx), safe_inv(dy),
+	traverse_nearest<true>(S.nodes, pre.tris, g.origin[0], g.origin[1], g.origin[2], dx, dy, dz, safe_inv(dx), safe_inv(dy),
 						   safe_inv(dz), h, tc);
 	pc.primary = 1;
 	__syncwarp();
@@ -187,7 +187,7 @@ __global__ void __launch_bounds__(256, SNL_WF_MIN_BLOCKS) k_wf_trace(SceneDev S,
 					dz = r.z;
 					h.dist = r.w;  // tmax
 					const PreSet ps = B.lightSets[li];
-					nodes = kRelNodes ? ps.nodes : S.nodes;
+					nodes = S.nodes;
 					ox = S.lights[li].pos[0];  // the shadow rays start at the light (box_test needs the origin)
 					oy = S.lights[li].pos[1];
 					oz = S.lights[li].pos[2];
@@ -226,11 +226,8 @@ __global__ void __launch_bounds__(256, SNL_WF_MIN_BLOCKS) k_wf_trace(SceneDev S,
 			bool h0, h1;
 			float lmin0, lmin1;
 			int l0, l1;
-#ifndef SNL_BOX_EXACT  // box_test takes origin * idir (loop-invariant: hoisted out of the walk)
-			node_test<SHADOW && kRelNodes>(nodes + cur, ox * ix, oy * iy, oz * iz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
-#else
-			node_test<SHADOW && kRelNodes>(nodes + cur, ox, oy, oz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
-#endif
+			// box_test takes origin * idir (loop-invariant: hoisted out of the walk)
+			node_test(nodes + cur, ox * ix, oy * iy, oz * iz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
 			SNL_TRAVERSE_STEP();
 			if(!__any_sync(__activemask(), leaf == 0))
 				break;
@@ -274,7 +271,7 @@ __global__ void __launch_bounds__(256, SNL_WF_MIN_BLOCKS) k_wf_trace(SceneDev S,
 			idle = true;
 		}
 	}
-	PacketCounts pc = {0, 0, 0, 0, 0};
+	PacketCounts pc = {};
 	__syncwarp();
 	flush_counts(S, pc, tc);
 }
@@ -284,7 +281,7 @@ __global__ void __launch_bounds__(kPacket) k_wf_shade(SceneDev S, WfBuffers B) {
 	const unsigned id = blockIdx.x * kPacket + threadIdx.x;
 	const float4 o = ld4(B.rayO + id), d = ld4(B.rayD + id);
 	const bool active = o.w != 0.0f;  // sel of level 0
-	PacketCounts pc = {0, 0, 0, 0, 0};
+	PacketCounts pc = {};
 	TravCount tc = {0, 0, 0};
 	Hit h;
 	h.dist = CUDART_INF_F;

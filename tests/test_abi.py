@@ -38,7 +38,7 @@ def test_struct_layouts_match_the_header(sb):
     assert C.sizeof(sb.Camera) == 13 * 4
     assert C.sizeof(sb.Light) == 36  # src/light.h: 9 floats
     assert C.sizeof(sb.api.Material) == 4 * 11
-    assert C.sizeof(sb.Stats) == 9 * 8 + 8  # 9 u64 + float (padded)
+    assert C.sizeof(sb.Stats) == 10 * 8 + 8  # 10 u64 + float (padded)
     assert sb.NODE_DTYPE.itemsize == 32 and sb.TRI_DTYPE.itemsize == 64 and sb.SHTRI_DTYPE.itemsize == 64
 
 
