@@ -402,7 +402,10 @@ def run_ours(args, w, W, H):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     t0 = time.time()
-    n_sus = max(1, int(args.sustain / max(1e-4, (sum(ms) / len(ms)) * 1e-3)))  # same frame count on every rank
+    mean_ms = torch.tensor([sum(ms) / len(ms)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(mean_ms, op=dist.ReduceOp.MAX)  # the SAME frame count on every rank: the render call is collective
+    n_sus = max(1, int(args.sustain / max(1e-4, float(mean_ms[0]) * 1e-3)))
     for k in range(n_sus):
         if fm is None:
             sc.render_dev(cam, W, H, frame, pitch, rank=rank)
