@@ -310,7 +310,8 @@ def run_ours(args, w, W, H):
     torch.cuda.set_device(dev)
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
 
     sc = sb.Scene(local_rank)
     sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"])
