@@ -209,52 +209,26 @@ __device__ __forceinline__ void node_test(const GpuNode *__restrict__ n, float o
 	h1 = box_test(b1.x, b1.y, b1.z, b1.w, bz.z, bz.w, ox, oy, oz, ix, iy, iz, dist, lmin1);
 }
 
-// WARP form of the two walks below (k_render / k_raytrace): ALL 32 lanes of the warp call, rays that are not traced
-// come with active = false and start at the sentinel. Both loops are then warp-uniform, so the per-step vote is one
-// full-mask VOTE instead of activemask + vote + divergence check (4 of the ~65 instructions of a step), and no lane
-// leaves the node loop on its own. Which lanes step when is unchanged: a lane walks while it has an inner node and some
-// lane of the warp still looks for its first leaf.
-#ifndef SNL_WARP_VOTE
-#define SNL_WARP_VOTE 1
-#endif
-constexpr bool kWarpVote = SNL_WARP_VOTE != 0;
-
 // BVH::TraversePrimaryN per ray (src/bvh/traverse.cpp:14-80).
-template <bool SHARED, bool SHORDER = false, bool WARP = false>
+template <bool SHARED, bool SHORDER = false>
 __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nodes, const void *__restrict__ tris,
 												 float ox, float oy, float oz, float dx, float dy, float dz, float ix,
-												 float iy, float iz, Hit &h, TravCount &tc, bool active = true) {
+												 float iy, float iz, Hit &h, TravCount &tc) {
 	SNL_STACK_DECL();
-	int cur = (WARP && !active) ? kSentinel : 0;
+	int cur = 0;
 	const float bx = ox * ix, by = oy * iy, bz = oz * iz;  // box_test's origin * idir
-	while(WARP ? __any_sync(SNL_FULL, cur != kSentinel) : cur != kSentinel) {
+	while(cur != kSentinel) {
 		int leaf = 0;  // parked leaf link (< 0), 0 = none
-		if(WARP) {
-			for(;;) {
-				const bool inner = (unsigned)cur < (unsigned)kSentinel;
-				if(!__any_sync(SNL_FULL, inner && leaf == 0))
-					break;
-				if(inner) {
-					SNL_COUNT(tc.nodes);
-					bool h0, h1;
-					float lmin0, lmin1;
-					int l0, l1;
-					node_test(nodes + cur, bx, by, bz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
-					SNL_TRAVERSE_STEP();
-				}
-			}
+		while((unsigned)cur < (unsigned)kSentinel) {
+			SNL_COUNT(tc.nodes);
+			bool h0, h1;
+			float lmin0, lmin1;
+			int l0, l1;
+			node_test(nodes + cur, bx, by, bz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
+			SNL_TRAVERSE_STEP();
+			if(!__any_sync(__activemask(), leaf == 0))
+				break;
 		}
-		else
-			while((unsigned)cur < (unsigned)kSentinel) {
-				SNL_COUNT(tc.nodes);
-				bool h0, h1;
-				float lmin0, lmin1;
-				int l0, l1;
-				node_test(nodes + cur, bx, by, bz, ix, iy, iz, h.dist, h0, h1, lmin0, lmin1, l0, l1);
-				SNL_TRAVERSE_STEP();
-				if(!__any_sync(__activemask(), leaf == 0))
-					break;
-			}
 #ifdef SNL_STEP_ONEPOP
 		if(leaf == 0 && cur < 0) {
 			leaf = cur;
@@ -285,42 +259,26 @@ __device__ __forceinline__ void traverse_nearest(const GpuNode *__restrict__ nod
 // (src/triangle.cpp:65-102): any hit, ONE-SIDED (only triangles with dir.nrm >= u+v >= 0 occlude), no division.
 // Origin = light position; triangles = that light's PreTri records, or (GEN, instanced scenes: the light seen from
 // inside an instance) the GenTri records with the sharedOrigin precomputation (src/triangle.cpp:13-18) done on the fly.
-template <bool GEN = false, bool WARP = false>
+template <bool GEN = false>
 __device__ __forceinline__ bool traverse_shadow(const GpuNode *__restrict__ nodes, const void *__restrict__ tris, float ox,
 												float oy, float oz, float dx, float dy, float dz, float ix, float iy, float iz,
-												float dist, TravCount &tc, bool active = true) {
+												float dist, TravCount &tc) {
 	const float bx = ox * ix, by = oy * iy, bz = oz * iz;  // box_test's origin * idir
 	SNL_STACK_DECL();
-	int cur = (WARP && !active) ? kSentinel : 0;
+	int cur = 0;
 	bool occluded = false;
-	while(WARP ? __any_sync(SNL_FULL, cur != kSentinel) : cur != kSentinel) {
+	while(cur != kSentinel) {
 		int leaf = 0;
-		if(WARP) {
-			for(;;) {
-				const bool inner = (unsigned)cur < (unsigned)kSentinel;
-				if(!__any_sync(SNL_FULL, inner && leaf == 0))
-					break;
-				if(inner) {
-					SNL_COUNT(tc.nodes);
-					bool h0, h1;
-					float lmin0, lmin1;
-					int l0, l1;
-					node_test(nodes + cur, bx, by, bz, ix, iy, iz, dist, h0, h1, lmin0, lmin1, l0, l1);
-					SNL_TRAVERSE_STEP();
-				}
-			}
+		while((unsigned)cur < (unsigned)kSentinel) {
+			SNL_COUNT(tc.nodes);
+			bool h0, h1;
+			float lmin0, lmin1;
+			int l0, l1;
+			node_test(nodes + cur, bx, by, bz, ix, iy, iz, dist, h0, h1, lmin0, lmin1, l0, l1);
+			SNL_TRAVERSE_STEP();
+			if(!__any_sync(__activemask(), leaf == 0))
+				break;
 		}
-		else
-			while((unsigned)cur < (unsigned)kSentinel) {
-				SNL_COUNT(tc.nodes);
-				bool h0, h1;
-				float lmin0, lmin1;
-				int l0, l1;
-				node_test(nodes + cur, bx, by, bz, ix, iy, iz, dist, h0, h1, lmin0, lmin1, l0, l1);
-				SNL_TRAVERSE_STEP();
-				if(!__any_sync(__activemask(), leaf == 0))
-					break;
-			}
 #ifdef SNL_STEP_ONEPOP
 		if(leaf == 0 && cur < 0) {
 			leaf = cur;
@@ -769,26 +727,13 @@ __device__ __forceinline__ void light_accumulate(const DevLight &L, float dot, f
 	lsb += L.color[2] * specMul;
 }
 
-// Returns true when a shadow ray was cast. WARP: called by all 32 lanes of the warp (see traverse_nearest).
-template <bool INST = false, bool WARP = false>
+// Returns true when a shadow ray was cast.
+template <bool INST = false>
 __device__ __forceinline__ bool trace_light(const SceneDev &S, int li, bool sel, const Sample &s, float &ldr, float &ldg,
 											float &ldb, float &lsr, float &lsg, float &lsb, TravCount &tc) {
-	const DevLight &L = S.lights[li];
-	if(WARP && !INST) {
-		float fx, fy, fz, dot, distance;
-		const bool cast = light_setup(L, s.px, s.py, s.pz, s.nx, s.ny, s.nz, fx, fy, fz, dot, distance) && sel;
-		const float tmax = distance * 0.9999f;
-		// beyond the light's radius the ray counts as traced but cannot change the sums: no walk (see below)
-		const float atten = light_attenuation(L, distance);
-		const bool walk = cast && atten > 0.0f;
-		const bool occluded = traverse_shadow<false, true>(S.nodes, S.lightPre[li].tris, L.pos[0], L.pos[1], L.pos[2], fx, fy, fz,
-														   safe_inv(fx), safe_inv(fy), safe_inv(fz), tmax, tc, walk);
-		if(walk && !occluded && tmax > 0.0f)
-			light_accumulate(L, dot, atten, ldr, ldg, ldb, lsr, lsg, lsb);
-		return cast;
-	}
 	if(!sel)
 		return false;
+	const DevLight &L = S.lights[li];
 	float fx, fy, fz, dot, distance;
 	if(!light_setup(L, s.px, s.py, s.pz, s.nx, s.ny, s.nz, fx, fy, fz, dot, distance))
 		return false;
@@ -1042,23 +987,14 @@ __device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet o
 	h.obj = 0;
 	h.inst = 0;
 	h.bu = h.bv = 0.0f;
-	if(kWarpVote && !INST) {  // every lane of the warp is here: warp-uniform walk, `active` rides along
-		const float ix = safe_inv(dx), iy = safe_inv(dy), iz = safe_inv(dz);
-		if(SHARED)
-			traverse_nearest<true, false, true>(S.nodes, originPre.tris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc, active);
-		else
-			traverse_nearest<false, false, true>(S.nodes, S.gtris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc, active);
-	}
 	if(active) {
-		if(!(kWarpVote && !INST)) {
-			const float ix = safe_inv(dx), iy = safe_inv(dy), iz = safe_inv(dz);
-			if(INST)
-				traverse_nearest_inst<SHARED>(S, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
-			else if(SHARED)
-				traverse_nearest<true>(S.nodes, originPre.tris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
-			else
-				traverse_nearest<false>(S.nodes, S.gtris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
-		}
+		const float ix = safe_inv(dx), iy = safe_inv(dy), iz = safe_inv(dz);
+		if(INST)
+			traverse_nearest_inst<SHARED>(S, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
+		else if(SHARED)
+			traverse_nearest<true>(S.nodes, originPre.tris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
+		else
+			traverse_nearest<false>(S.nodes, S.gtris, ox, oy, oz, dx, dy, dz, ix, iy, iz, h, tc);
 		if(!DEPTH0)
 			pc.transparency++;
 		else if(LEVEL == 0)
@@ -1127,7 +1063,7 @@ __device__ __forceinline__ bool raytrace_level(const SceneDev &S, const PreSet o
 			// the packet's hit points are all farther from this light than its radius: src/scene_trace.cpp:498-499
 			if(!DEFER && cullable && box_point_distance_sq(boxLo, boxHi, S.lights[li].pos) > S.lights[li].radSq)
 				continue;
-			const bool cast = trace_light<INST, kWarpVote>(S, li, sel, s, ldr, ldg, ldb, lsr, lsg, lsb, tc);
+			const bool cast = trace_light<INST>(S, li, sel, s, ldr, ldg, ldb, lsr, lsg, lsb, tc);
 			if(DEFER && cullable) {
 				const unsigned m = __ballot_sync(SNL_FULL, cast);
 				if((threadIdx.x & 31) == 0 && m)
