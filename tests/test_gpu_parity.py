@@ -250,7 +250,7 @@ def test_raytrace_packets_vs_oracle(sb):
         err = np.abs(rgb_g - rgb_r).max(axis=1)
         frac = float((err <= 1.0 / 255).mean())
         print(f"raytrace mask={m is not None} shared={shared}: within 1/255: {frac*100:.3f}% exact {(err==0).mean()*100:.3f}% rays {st['rays']} ref {rays_r}")
-        assert frac >= 0.995
+        assert frac >= 0.999  # north_star's image criterion, per ray; measured: 100 % identical (tools/diag_raytrace.py)
 
 
 def test_tiles_and_device_output(sb):
