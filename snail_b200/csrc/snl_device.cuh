@@ -169,36 +169,6 @@ enum { kSentinel = 0x7fffffff };
 #else
 // Default: plain stack in local memory, [0] = sentinel. Fewer instructions per step than the register-cached top
 // (SNL_STEP_TOS, which the wavefront kernels keep), one more dependent LDL on a double pop: 0.5 % faster on B200.
-// SNL_SMEM_STACK = K > 0 (A/B switch): the first K stack slots live in shared memory laid out [slot][thread] - bank =
-// thread, so a push / pop of a divergent warp is ONE L1 wavefront where the local-memory stack costs one per distinct
-// slot index among the lanes; deeper slots fall back to local memory.
-#ifndef SNL_SMEM_STACK
-#define SNL_SMEM_STACK 0
-#endif
-#if SNL_SMEM_STACK > 0
-__device__ __forceinline__ int *smem_stack() {
-	__shared__ int s[SNL_SMEM_STACK * kPacket];
-	return s;
-}
-#define SNL_STACK_DECL()                           \
-	int lstack[kStack + 1];                        \
-	int *const sbase = smem_stack() + threadIdx.x; \
-	sbase[0] = kSentinel;                          \
-	int sp = 1
-#define SNL_PUSH(v)                              \
-	do {                                         \
-		if(sp < SNL_SMEM_STACK)                  \
-			sbase[sp * kPacket] = (v);           \
-		else                                     \
-			lstack[sp - SNL_SMEM_STACK] = (v);   \
-		sp++;                                    \
-	} while(0)
-#define SNL_POP(dst)                                                                   \
-	do {                                                                               \
-		--sp;                                                                          \
-		dst = sp < SNL_SMEM_STACK ? sbase[sp * kPacket] : lstack[sp - SNL_SMEM_STACK]; \
-	} while(0)
-#else
 // The stack top is a POINTER into local memory: a push / pop is STL / LDL + one add, without the index -> address LEA
 // (+1.8 % on sponza_like against an index).
 #define SNL_STACK_DECL()   \
@@ -207,7 +177,6 @@ __device__ __forceinline__ int *smem_stack() {
 	int *sp = stack + 1
 #define SNL_PUSH(v) *sp++ = (v)
 #define SNL_POP(dst) dst = *--sp
-#endif
 #define SNL_STEP_ONEPOP
 // One pop site per step: a leaf that gets parked and a step that hit nothing both take the next stack entry. (A popped
 // entry that is itself a leaf ends the inner walk even when nothing is parked yet; the triangle loop takes it from cur.)

@@ -97,4 +97,6 @@ def test_rays_and_shadow_vs_golden(sb, name):
     sc.set_lights([sb.Light(lg[0:3], lg[3:6], lg[6])])
     rgb, st = sc.raytrace(g["ray_o"], g["ray_d"], None)
     err = np.abs(rgb - g["rt_rgb"]).max(axis=1)
+    print(f"{name}: snl_raytrace vs golden: within 1/255 on {float((err <= 1.0 / 255).mean())*100:.3f} % of {len(err)} rays, "
+          f"identical {float((err == 0).mean())*100:.3f} %; worst {np.sort(err)[-5:]}")
     assert float((err <= 1.0 / 255).mean()) >= 0.999
