@@ -17,6 +17,7 @@
 //   rank 0   k_wait_counter + cudaMemcpy2DAsync per row band on copy streams: band i goes to the host while band i+1
 //            is still being rendered; then the summed stats.
 // Every wait has a time-out that raises CommCtl::error instead of hanging the device.
+#include <cstdlib>
 #include <cstring>
 
 #include "snl_scene.h"
@@ -356,11 +357,14 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 		d.bandDone = ctl->bandDone[slot];
 		d.ready = &ctl->ready[slot];
 		d.readyVal = seq + 1u;
-		d.nPackets = nPackets;
-		// batches of a few packets while there are plenty per resident CTA, single packets once the GPUs would starve
+		// a few packets per fetch while there are plenty per resident CTA (one release fence per batch), single packets
+		// once the GPUs would starve; SNL_DYN_BATCH overrides (tuning)
 		const unsigned perCta = nPackets / std::max(1u, (unsigned)(ctas * c->world));
-		d.batch = perCta >= 16 ? 4u : perCta >= 8 ? 2u : 1u;
-		d.nBatches = (nPackets + d.batch - 1) / d.batch;
+		d.batch = perCta >= 32 ? 8u : perCta >= 12 ? 4u : perCta >= 6 ? 2u : 1u;
+		if(const char *e = getenv("SNL_DYN_BATCH"))
+			d.batch = (unsigned)std::max(1, std::min(64, atoi(e)));
+		d.nBatches = (unsigned)(((px + (int)d.batch - 1) / (int)d.batch) * py);
+		d.local = r.rank == 0 ? 1u : 0u;
 		d.rowsPerBand = (unsigned)c->rowsPerBand;
 		d.error = &ctl->error;
 		SNL_CUDA(launch_render(S, s->originPre.set(), g, W, H, nullptr, 0, frame, c->pitch, variant, s->stream, 0, -1, &d, ctas));

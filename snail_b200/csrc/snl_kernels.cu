@@ -300,35 +300,50 @@ __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreS
 			store_tile(tile, px0, py0, cw, ch, out, pitch);
 		return;
 	}
+	// Batches are runs of ctl.batch consecutive packets of ONE packet row (so a batch never straddles a row band) and are
+	// handed out in row-major order by the shared cursor. Thread 0 keeps one fetch in flight: the index of the next batch
+	// is requested when the current one starts, so the NVLink round trip of the atomic hides behind the packets.
 	__shared__ unsigned sBatch;
+	unsigned long long pending = ~0ull;  // thread 0: cursor value of the batch after the current one
 	if(threadIdx.x == 0) {
 		// the frame slot is opened by rank 0 (k_frame_open) once every rank has left the frame that used it before
-		sBatch = wait_sys<false>(ctl.ready, ctl.readyVal, ctl.error) ? 0u : 0xffffffffu;
+		if(wait_sys<false>(ctl.ready, ctl.readyVal, ctl.error))
+			pending = atomicAdd_system(ctl.cursor, 1ull);
 	}
+	const unsigned perRow = (unsigned)(packetsX + (int)ctl.batch - 1) / ctl.batch;  // batches per packet row
 	for(;;) {
-		__syncthreads();
-		if(threadIdx.x == 0 && sBatch != 0xffffffffu) {
-			const unsigned long long b = atomicAdd_system(ctl.cursor, 1ull);
-			sBatch = b < ctl.nBatches ? (unsigned)b : 0xfffffffeu;
+		__syncthreads();  // the previous batch is done with sBatch and `tile`
+		if(threadIdx.x == 0) {
+			const bool have = pending < (unsigned long long)ctl.nBatches;
+			sBatch = have ? (unsigned)pending : 0xffffffffu;
+			if(have)
+				pending = atomicAdd_system(ctl.cursor, 1ull);
 		}
 		__syncthreads();
 		const unsigned b = sBatch;
-		if(b >= ctl.nBatches)
+		if(b == 0xffffffffu)
 			break;
-		const unsigned first = b * ctl.batch, count = min(ctl.batch, ctl.nPackets - first);
-		for(unsigned k = 0; k < count; k++) {
-			const int packet = (int)(first + k);
-			const int px0 = (packet % packetsX) * 16, py0 = (packet / packetsX) * 16;
+		const int row = (int)(b / perRow), col0 = (int)((b - (unsigned)row * perRow) * ctl.batch);
+		const int count = min((int)ctl.batch, packetsX - col0);
+		for(int k = 0; k < count; k++) {
+			const int px0 = (col0 + k) * 16, py0 = row * 16;
 			const int cw = min(16, W - px0), ch = min(16, H - py0);
+			if(k)
+				__syncthreads();  // `tile` of the previous packet has been stored
 			render_packet<FLAGS, SUPER>(S, pre, g, px0, py0, cw, ch, out, pitch, tile, pc, tc);
 			__syncthreads();
 			if(!SUPER)
 				store_tile(tile, px0, py0, cw, ch, out, pitch);
-			__syncthreads();  // every pixel of the packet is on its way, `tile` is free again
-			if(threadIdx.x == 0) {
+		}
+		__syncthreads();  // every pixel of the batch is on its way
+		if(threadIdx.x == 0) {
+			// release the batch to rank 0's copy streams: rank 0 itself only needs device scope (frame, counters and the
+			// waiting kernel all live on its GPU); a peer's stores cross NVLink and need the system-scope fence
+			if(ctl.local)
+				__threadfence();
+			else
 				__threadfence_system();
-				atomicAdd_system(ctl.bandDone + min((unsigned)(py0 >> 4) / ctl.rowsPerBand, (unsigned)kCommBands - 1u), 1u);
-			}
+			atomicAdd_system(ctl.bandDone + min((unsigned)row / ctl.rowsPerBand, (unsigned)kCommBands - 1u), (unsigned)count);
 		}
 	}
 	flush_counts(S, pc, tc);

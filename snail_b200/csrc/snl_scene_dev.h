@@ -58,8 +58,9 @@ struct DynCtl {
 	unsigned *bandDone;     // [kCommBands] of this frame's slot
 	const unsigned *ready;  // fetch only once *ready == readyVal
 	unsigned readyVal;
-	unsigned nBatches, batch, nPackets;
+	unsigned nBatches, batch;  // batches of the frame (row-aligned runs of `batch` packets), packets per batch
 	unsigned rowsPerBand;   // packet rows per band
+	unsigned local;         // this rank owns the frame and the counters: device-scope release is enough
 	unsigned *error;
 };
 
