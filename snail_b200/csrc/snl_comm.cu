@@ -53,6 +53,7 @@ struct CommRank {  // one rank driven by this process
 	int rank = 0;
 	unsigned char *seg = nullptr;  // rank 0's segment as this rank's device sees it
 	bool ipc = false;              // mapped with cudaIpcOpenMemHandle (else: owned, or a peer pointer of this process)
+	unsigned *localReady = nullptr;  // device-local: "frame slot seen open" note shared by this rank's CTAs
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
 
@@ -113,6 +114,8 @@ int comm_root_resources(snl_comm *c) {
 
 int comm_rank_events(CommRank &r) {
 	SNL_CUDA(cudaSetDevice(r.scene->device));
+	SNL_CUDA(cudaMalloc((void **)&r.localReady, 2 * sizeof(unsigned)));
+	SNL_CUDA(cudaMemset(r.localReady, 0, 2 * sizeof(unsigned)));
 	SNL_CUDA(cudaEventCreate(&r.ev0));
 	SNL_CUDA(cudaEventCreate(&r.ev1));
 	return SNL_OK;
@@ -274,6 +277,8 @@ void snl_comm_destroy(snl_comm *c) {
 			cudaEventDestroy(r.ev1);
 		if(r.ipc && r.seg)
 			cudaIpcCloseMemHandle(r.seg);
+		if(r.localReady)
+			cudaFree(r.localReady);
 	}
 	if(!c->ranks.empty() && c->ranks[0].rank == 0 && c->ranks[0].scene) {
 		cudaSetDevice(c->ranks[0].scene->device);
@@ -351,19 +356,16 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 			s->launches++;
 		}
 		const int variant = std::max(0, s->tune.choice);
-		const int ctas = s->smCount * render_ctas_per_sm(S, variant);
+		// one CTA per packet this rank can take: its share plus a third (the ranks are alike: what varies is the cost of the
+		// packets they happen to draw), all of them when it renders alone. CTAs that find the frame handed out exit at once.
+		const int ctas = c->world == 1 ? (int)nPackets : (int)std::min<size_t>(nPackets, (size_t)nPackets * 4 / (3 * c->world) + 2 * s->smCount);
 		DynCtl d;
 		d.cursor = &ctl->cursor[slot];
 		d.bandDone = ctl->bandDone[slot];
 		d.ready = &ctl->ready[slot];
+		d.localReady = r.localReady + slot;
 		d.readyVal = seq + 1u;
-		// a few packets per fetch while there are plenty per resident CTA (one release fence per batch), single packets
-		// once the GPUs would starve; SNL_DYN_BATCH overrides (tuning)
-		const unsigned perCta = nPackets / std::max(1u, (unsigned)(ctas * c->world));
-		d.batch = perCta >= 32 ? 8u : perCta >= 12 ? 4u : perCta >= 6 ? 2u : 1u;
-		if(const char *e = getenv("SNL_DYN_BATCH"))
-			d.batch = (unsigned)std::max(1, std::min(64, atoi(e)));
-		d.nBatches = (unsigned)(((px + (int)d.batch - 1) / (int)d.batch) * py);
+		d.nPackets = nPackets;
 		d.local = r.rank == 0 ? 1u : 0u;
 		d.rowsPerBand = (unsigned)c->rowsPerBand;
 		d.error = &ctl->error;

@@ -1187,12 +1187,9 @@ template <bool GE> __device__ __forceinline__ bool wait_sys(const unsigned *p, u
 	}
 }
 
-// CTA-level aggregation of the per-lane ray counters into the scene's global counters.
-__device__ __forceinline__ void flush_counts(const SceneDev &S, const PacketCounts &pc, const TravCount &tc) {
-	__shared__ unsigned sh[kCounters];
-	if(threadIdx.x < kCounters)
-		sh[threadIdx.x] = 0;
-	__syncthreads();
+// CTA-level aggregation of the per-lane ray counters: warp sums go to `sh` (shared, kCounters entries, zeroed by the
+// caller before a barrier) ...
+__device__ __forceinline__ void counts_to_shared(const PacketCounts &pc, const TravCount &tc, unsigned *sh) {
 	unsigned v[kCounters] = {pc.primary, pc.shadow, pc.reflection, pc.reflection_shadow, tc.nodes, tc.tris, tc.gtris, pc.transparency,
 							 pc.truncated};
 #pragma unroll
@@ -1204,9 +1201,20 @@ __device__ __forceinline__ void flush_counts(const SceneDev &S, const PacketCoun
 		if((threadIdx.x & 31) == 0 && x)
 			atomicAdd(&sh[i], x);
 	}
-	__syncthreads();
+}
+// ... and from there (after a barrier) into the scene's global counters.
+__device__ __forceinline__ void counts_to_global(const SceneDev &S, const unsigned *sh) {
 	if(threadIdx.x < kCounters && sh[threadIdx.x])
 		atomicAdd(reinterpret_cast<unsigned long long *>(S.counters) + threadIdx.x, (unsigned long long)sh[threadIdx.x]);
+}
+__device__ __forceinline__ void flush_counts(const SceneDev &S, const PacketCounts &pc, const TravCount &tc) {
+	__shared__ unsigned sh[kCounters];
+	if(threadIdx.x < kCounters)
+		sh[threadIdx.x] = 0;
+	__syncthreads();
+	counts_to_shared(pc, tc, sh);
+	__syncthreads();
+	counts_to_global(S, sh);
 }
 
 }  // namespace snl

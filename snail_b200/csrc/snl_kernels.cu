@@ -273,80 +273,66 @@ template <int FLAGS, bool SUPER, int MINB, bool DYN>
 __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreSet pre, RayGenParams g, int W, int H,
 												 int packetsX, const int4 *__restrict__ packets,
 												 unsigned char *__restrict__ out, size_t pitch, int firstPacket, const DynCtl ctl) {
-	PacketCounts pc = {};
-	TravCount tc = {0, 0, 0};
 	__shared__ __align__(16) unsigned char tile[SUPER ? 16 : 16 * 48];
-	if(S.hasUber)
-		packet_vote_init();
-	if(!DYN) {
-		int px0, py0, cw, ch;
-		const int packet = blockIdx.x + firstPacket;
-		if(packets) {
-			const int4 p = packets[packet];
-			px0 = p.x;
-			py0 = p.y;
-			cw = p.z;
-			ch = p.w;
-		}
-		else {
-			px0 = (packet % packetsX) * 16;
-			py0 = (packet / packetsX) * 16;
-			cw = min(16, W - px0);
-			ch = min(16, H - py0);
-		}
-		render_packet<FLAGS, SUPER>(S, pre, g, px0, py0, cw, ch, out, pitch, tile, pc, tc);
-		flush_counts(S, pc, tc);  // its barriers also publish `tile`
-		if(!SUPER)
-			store_tile(tile, px0, py0, cw, ch, out, pitch);
-		return;
-	}
-	// Batches are runs of ctl.batch consecutive packets of ONE packet row (so a batch never straddles a row band) and are
-	// handed out in row-major order by the shared cursor. Thread 0 keeps one fetch in flight: the index of the next batch
-	// is requested when the current one starts, so the NVLink round trip of the atomic hides behind the packets.
-	__shared__ unsigned sBatch;
-	unsigned long long pending = ~0ull;  // thread 0: cursor value of the batch after the current one
-	if(threadIdx.x == 0) {
-		// the frame slot is opened by rank 0 (k_frame_open) once every rank has left the frame that used it before
-		if(wait_sys<false>(ctl.ready, ctl.readyVal, ctl.error))
-			pending = atomicAdd_system(ctl.cursor, 1ull);
-	}
-	const unsigned perRow = (unsigned)(packetsX + (int)ctl.batch - 1) / ctl.batch;  // batches per packet row
-	for(;;) {
-		__syncthreads();  // the previous batch is done with sBatch and `tile`
+	int packet = blockIdx.x + firstPacket;
+	if(DYN) {
+		// Multi-GPU frame: the CTA takes the next packet of the frame from the cursor all ranks share (system-scope atomic
+		// in rank 0's memory) instead of its block index, so the GPUs balance themselves packet by packet. Still one
+		// packet per CTA - a persistent loop costs the packet registers (+6 % per frame, measured) and coarser batches
+		// leave a tail (runs of 8 packets: +60 %); the other resident CTAs of the SM cover the fetch latency.
+		__shared__ unsigned sPacket;
 		if(threadIdx.x == 0) {
-			const bool have = pending < (unsigned long long)ctl.nBatches;
-			sBatch = have ? (unsigned)pending : 0xffffffffu;
-			if(have)
-				pending = atomicAdd_system(ctl.cursor, 1ull);
+			unsigned p = 0xffffffffu;
+			// the frame slot is opened by rank 0 (k_frame_open) once every rank has left the frame that used it before;
+			// the first CTA of this rank that sees it open leaves a note in local memory for the others
+			bool open = *(volatile unsigned *)ctl.localReady == ctl.readyVal;
+			if(!open && wait_sys<false>(ctl.ready, ctl.readyVal, ctl.error)) {
+				*(volatile unsigned *)ctl.localReady = ctl.readyVal;
+				open = true;
+			}
+			if(open)
+				p = atomicAdd_system(ctl.cursor, 1u);
+			sPacket = p < ctl.nPackets ? p : 0xffffffffu;
 		}
 		__syncthreads();
-		const unsigned b = sBatch;
-		if(b == 0xffffffffu)
-			break;
-		const int row = (int)(b / perRow), col0 = (int)((b - (unsigned)row * perRow) * ctl.batch);
-		const int count = min((int)ctl.batch, packetsX - col0);
-		for(int k = 0; k < count; k++) {
-			const int px0 = (col0 + k) * 16, py0 = row * 16;
-			const int cw = min(16, W - px0), ch = min(16, H - py0);
-			if(k)
-				__syncthreads();  // `tile` of the previous packet has been stored
-			render_packet<FLAGS, SUPER>(S, pre, g, px0, py0, cw, ch, out, pitch, tile, pc, tc);
-			__syncthreads();
-			if(!SUPER)
-				store_tile(tile, px0, py0, cw, ch, out, pitch);
-		}
-		__syncthreads();  // every pixel of the batch is on its way
+		if(sPacket == 0xffffffffu)
+			return;  // the frame has been handed out (this rank launches a few CTAs more than its share)
+		packet = (int)sPacket;
+	}
+	PacketCounts pc = {};
+	TravCount tc = {0, 0, 0};
+	if(S.hasUber)
+		packet_vote_init();
+	int px0, py0, cw, ch;
+	if(packets) {
+		const int4 p = packets[packet];
+		px0 = p.x;
+		py0 = p.y;
+		cw = p.z;
+		ch = p.w;
+	}
+	else {
+		px0 = (packet % packetsX) * 16;
+		py0 = (packet / packetsX) * 16;
+		cw = min(16, W - px0);
+		ch = min(16, H - py0);
+	}
+	render_packet<FLAGS, SUPER>(S, pre, g, px0, py0, cw, ch, out, pitch, tile, pc, tc);
+	flush_counts(S, pc, tc);  // its barriers also publish `tile`
+	if(!SUPER)
+		store_tile(tile, px0, py0, cw, ch, out, pitch);
+	if(DYN) {
+		__syncthreads();  // every pixel of the packet is on its way
 		if(threadIdx.x == 0) {
-			// release the batch to rank 0's copy streams: rank 0 itself only needs device scope (frame, counters and the
+			// release the packet to rank 0's copy streams: rank 0 itself only needs device scope (frame, counters and the
 			// waiting kernel all live on its GPU); a peer's stores cross NVLink and need the system-scope fence
 			if(ctl.local)
 				__threadfence();
 			else
 				__threadfence_system();
-			atomicAdd_system(ctl.bandDone + min((unsigned)row / ctl.rowsPerBand, (unsigned)kCommBands - 1u), (unsigned)count);
+			atomicAdd_system(ctl.bandDone + min((unsigned)(py0 >> 4) / ctl.rowsPerBand, (unsigned)kCommBands - 1u), 1u);
 		}
 	}
-	flush_counts(S, pc, tc);
 }
 
 // ---- launch wrappers ------------------------------------------------------------------------------------------
@@ -416,7 +402,7 @@ cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenPara
 	int grid = count < 0 ? all - first : count;
 	DynCtl ctl;
 	memset(&ctl, 0, sizeof(ctl));
-	if(dyn) {  // persistent CTAs fetching packet batches from dyn->cursor
+	if(dyn) {  // `persistentCtas` CTAs, each fetching one packet from dyn->cursor
 		ctl = *dyn;
 		grid = persistentCtas;
 		first = 0;
@@ -472,7 +458,7 @@ __global__ void k_frame_open(CommCtl *ctl, unsigned seq, int world) {
 		wait_sys<true>(&ctl->rankDone[threadIdx.x], seq - 1u, &ctl->error);
 	__syncwarp();
 	if(threadIdx.x == 0) {
-		ctl->cursor[slot] = 0ull;
+		ctl->cursor[slot] = 0u;
 		ctl->statsArrived[slot] = 0u;
 	}
 	if(threadIdx.x < kCounters)

@@ -41,7 +41,7 @@ struct SceneDev {
 // peer access), all fields updated with system-scope atomics / release stores. Two frame slots alternate.
 enum { kCommBands = 8, kCommRanks = 16, kCommCtlBytes = 4096 };
 struct CommCtl {
-	unsigned long long cursor[2];               // next packet batch of the frame in this slot
+	unsigned cursor[2];                         // next packet of the frame in this slot
 	unsigned long long stats[2][kCounters];            // Counters of the frame summed over the ranks
 	unsigned bandDone[2][kCommBands];           // packets completed per row band
 	unsigned ready[2];                          // seq + 1 once the slot has been opened for frame seq
@@ -51,14 +51,15 @@ struct CommCtl {
 };
 static_assert(sizeof(CommCtl) <= kCommCtlBytes, "CommCtl must fit its page");
 
-// k_render's work source: cursor == null -> one packet per CTA (blockIdx + firstPacket); else persistent CTAs that fetch
-// batches of packets from the shared cursor and report every finished packet to its band's counter.
+// Work source of k_render<DYN>: every CTA fetches its packet from the cursor the ranks share and reports it to its
+// band's counter when its pixels are stored.
 struct DynCtl {
-	unsigned long long *cursor;
+	unsigned *cursor;
 	unsigned *bandDone;     // [kCommBands] of this frame's slot
 	const unsigned *ready;  // fetch only once *ready == readyVal
+	unsigned *localReady;   // this rank's own copy of that observation (device-local)
 	unsigned readyVal;
-	unsigned nBatches, batch;  // batches of the frame (row-aligned runs of `batch` packets), packets per batch
+	unsigned nPackets;
 	unsigned rowsPerBand;   // packet rows per band
 	unsigned local;         // this rank owns the frame and the counters: device-scope release is enough
 	unsigned *error;
