@@ -312,6 +312,19 @@ static const float kRankTint[16][3] = {  // src/render.cpp:119-128
 	{1.0f, 1.0f, 0.6f}, {1.0f, 1.0f, 1.0f}, {0.3f, 0.3f, 0.3f}, {0.3f, 0.3f, 1.0f}, {0.3f, 0.7f, 0.3f}, {0.3f, 0.7f, 0.7f},
 	{0.7f, 0.3f, 0.3f}, {0.7f, 0.3f, 0.7f}, {0.7f, 0.7f, 0.3f}, {0.7f, 1.7f, 0.7f}};
 
+// Row-band streams + events of a scene (snl_render's banded host copy, snl_render_multi), created on first use.
+int snl::ensure_band_streams(snl_scene *s) {
+	if(s->forkEv)
+		return SNL_OK;
+	SNL_CUDA(cudaSetDevice(s->device));
+	SNL_CUDA(cudaEventCreateWithFlags(&s->forkEv, cudaEventDisableTiming));
+	for(int b = 0; b < snl_scene::kMaxBands; b++) {
+		SNL_CUDA(cudaStreamCreateWithFlags(&s->bandStream[b], cudaStreamNonBlocking));
+		SNL_CUDA(cudaEventCreateWithFlags(&s->bandEv[b], cudaEventDisableTiming));
+	}
+	return SNL_OK;
+}
+
 // What one Render() call needs on the device before its k_render: the scene argument (lights, options, per-origin
 // triangle records of the camera and the lights, shared where a light sits at the camera) and the ray generator.
 int snl::prepare_frame(snl_scene *s, const snl_camera *cam, int W, int H, int rank, SceneDev &S, RayGenParams &g) {
@@ -1116,13 +1129,7 @@ static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, cons
 	const int nBands = bandsEnv ? std::min(atoi(bandsEnv), (int)snl_scene::kMaxBands)
 								: (s->lastCallMs > 0.8f ? (int)snl_scene::kMaxBands : (int)snl_scene::kBands);
 	if(hostOut && hostDone && !packets && nPk >= 8 * s->smCount && nBands > 1) {
-		if(!s->forkEv) {
-			SNL_CUDA(cudaEventCreateWithFlags(&s->forkEv, cudaEventDisableTiming));
-			for(int b = 0; b < snl_scene::kMaxBands; b++) {
-				SNL_CUDA(cudaStreamCreateWithFlags(&s->bandStream[b], cudaStreamNonBlocking));
-				SNL_CUDA(cudaEventCreateWithFlags(&s->bandEv[b], cudaEventDisableTiming));
-			}
-		}
+		SNL_TRY(ensure_band_streams(s));
 		const int px = (W + 15) / 16, py = (H + 15) / 16;
 		SNL_CUDA(cudaEventRecord(s->forkEv, s->stream));
 		for(int b = 0; b < nBands; b++) {

@@ -7,15 +7,20 @@
 //
 //     [ CommCtl (4 KB) | frame slot 0 | frame slot 1 ]
 //
-// Per frame `seq` (slot = seq & 1), everything in-stream, no host-side collective:
-//   rank 0   k_frame_open    waits until every rank has left frame seq-2, zeroes the slot's cursor / counters, opens it
-//   all      k_render        persistent CTAs; each fetches the next packet batch from the SHARED cursor with a
-//                            system-scope atomic (the reference's taskMap dealt tiles statically, src/server.cpp:238-248;
-//                            here the GPUs balance themselves), stores the packet into rank 0's frame over NVLink as
-//                            16-byte vectors and bumps the packet's band counter
-//   all      k_frame_publish adds the rank's TreeStats counters to the frame's (src/server.cpp:403-418), marks the rank done
-//   rank 0   k_wait_counter + cudaMemcpy2DAsync per row band on copy streams: band i goes to the host while band i+1
-//            is still being rendered; then the summed stats.
+// Work split: the frame's packets are dealt to the ranks in tiles of 4 packets (64 x 16 pixels), every run of `world`
+// consecutive tiles going to all ranks in a freshly shuffled order (the reference's taskMap, src/server.cpp:238-248),
+// and each rank's list is kept in row-band order. Per frame `seq` (slot = seq & 1), everything in-stream, no host-side
+// collective:
+//   rank 0   k_frame_open     waits until every rank has left frame seq-2, zeroes the slot's counters, opens it
+//   rank r   k_wait_counter   (r > 0) waits for the slot to be open
+//   all      per row band, on the band's own stream:  k_render of the rank's packets of that band, storing 16-byte
+//            vectors straight into rank 0's frame over NVLink, then k_band_signal: the kernel boundary has completed the
+//            launch's stores, so ONE system-scope increment per (rank, band) says the share is in - no fence and no
+//            atomic per packet (measured: a cursor-fed k_render with a release per packet cost 3 % on the headline and
+//            15-20 % on the cheap 4K frames on one GPU, and ~10 us per packet on a peer)
+//   rank 0   on the same band stream: k_wait_counter(band counter == world) + cudaMemcpy2DAsync of the band's rows: band
+//            i goes to the host while band i+1 is still being rendered on every GPU
+//   all      k_frame_publish  adds the rank's TreeStats counters to the frame's (src/server.cpp:403-418), marks the rank done
 // Every wait has a time-out that raises CommCtl::error instead of hanging the device.
 #include <cstdlib>
 #include <cstring>
@@ -53,7 +58,8 @@ struct CommRank {  // one rank driven by this process
 	int rank = 0;
 	unsigned char *seg = nullptr;  // rank 0's segment as this rank's device sees it
 	bool ipc = false;              // mapped with cudaIpcOpenMemHandle (else: owned, or a peer pointer of this process)
-	unsigned *localReady = nullptr;  // device-local: "frame slot seen open" note shared by this rank's CTAs
+	int4 *dPackets = nullptr;      // this rank's packets {x, y, w, h}, row bands in order
+	int bandFirst[kCommBands + 1] = {};  // [b] .. [b + 1]: its packets of band b
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
 
@@ -76,8 +82,6 @@ struct snl_comm {
 	bool ownsSegment = false;
 	// rank 0's side
 	int nBands = 1, rowsPerBand = 1;
-	cudaStream_t copyStream[kCommBands] = {};
-	cudaEvent_t copyEv[kCommBands] = {}, openEv = nullptr;
 	unsigned long long *hStats = nullptr;  // pinned: kCounters counters + error word
 	float lastMs = 0.0f;
 };
@@ -103,22 +107,16 @@ int comm_geometry(snl_comm *c, int world, int W, int H) {
 int comm_root_resources(snl_comm *c) {
 	CommRank &r0 = c->ranks[0];
 	SNL_CUDA(cudaSetDevice(r0.scene->device));
-	SNL_CUDA(cudaEventCreateWithFlags(&c->openEv, cudaEventDisableTiming));
-	for(int b = 0; b < c->nBands; b++) {
-		SNL_CUDA(cudaStreamCreateWithFlags(&c->copyStream[b], cudaStreamNonBlocking));
-		SNL_CUDA(cudaEventCreateWithFlags(&c->copyEv[b], cudaEventDisableTiming));
-	}
 	SNL_CUDA(cudaMallocHost(&c->hStats, 16 * sizeof(unsigned long long)));
 	return SNL_OK;
 }
 
 int comm_rank_events(CommRank &r) {
 	SNL_CUDA(cudaSetDevice(r.scene->device));
-	SNL_CUDA(cudaMalloc((void **)&r.localReady, 2 * sizeof(unsigned)));
-	SNL_CUDA(cudaMemset(r.localReady, 0, 2 * sizeof(unsigned)));
+
 	SNL_CUDA(cudaEventCreate(&r.ev0));
 	SNL_CUDA(cudaEventCreate(&r.ev1));
-	return SNL_OK;
+	return ensure_band_streams(r.scene);
 }
 
 int alloc_segment(snl_comm *c, snl_scene *s, unsigned char **seg) {
@@ -129,6 +127,48 @@ int alloc_segment(snl_comm *c, snl_scene *s, unsigned char **seg) {
 	SNL_CUDA(cudaDeviceSynchronize());
 	*seg = (unsigned char *)p;
 	c->ownsSegment = true;
+	return SNL_OK;
+}
+
+// The reference's taskMap (src/server.cpp:238-248): every run of `world` consecutive tiles goes to all ranks in a freshly
+// shuffled order. A fixed generator, so every process computes the same map without talking.
+std::vector<int> deal_tiles(int nTiles, int world) {
+	std::vector<int> owner(nTiles), order(world);
+	for(int i = 0; i < world; i++)
+		order[i] = i;
+	unsigned long long state = 0x9e3779b97f4a7c15ull;
+	for(int n = 0; n < nTiles; n++) {
+		if(n % world == 0)
+			for(int i = world - 1; i > 0; i--) {  // Fisher-Yates
+				state = state * 6364136223846793005ull + 1442695040888963407ull;
+				std::swap(order[i], order[(int)((state >> 33) % (unsigned)(i + 1))]);
+			}
+		owner[n] = order[n % world];
+	}
+	return owner;
+}
+
+enum { kTilePackets = 4 };  // a tile = 4 packets of one packet row (64 x 16 pixels)
+
+int build_packet_list(snl_comm *c, CommRank &r) {
+	const int W = c->W, H = c->H, px = (W + 15) / 16, py = (H + 15) / 16;
+	const int tilesX = (px + kTilePackets - 1) / kTilePackets;
+	const std::vector<int> owner = deal_tiles(tilesX * py, c->world);
+	std::vector<int4> list;
+	for(int b = 0; b < c->nBands; b++) {
+		r.bandFirst[b] = (int)list.size();
+		for(int row = b * c->rowsPerBand; row < std::min(py, (b + 1) * c->rowsPerBand); row++)
+			for(int t = 0; t < tilesX; t++)
+				if(owner[row * tilesX + t] == r.rank)
+					for(int col = t * kTilePackets; col < std::min(px, (t + 1) * kTilePackets); col++)
+						list.push_back(make_int4(col * 16, row * 16, std::min(16, W - col * 16), std::min(16, H - row * 16)));
+	}
+	for(int b = c->nBands; b <= kCommBands; b++)
+		r.bandFirst[b] = (int)list.size();
+	SNL_CUDA(cudaSetDevice(r.scene->device));
+	SNL_CUDA(cudaMalloc((void **)&r.dPackets, std::max<size_t>(list.size(), 1) * sizeof(int4)));
+	if(!list.empty())
+		SNL_CUDA(cudaMemcpy(r.dPackets, list.data(), list.size() * sizeof(int4), cudaMemcpyHostToDevice));
 	return SNL_OK;
 }
 
@@ -148,6 +188,8 @@ int snl_comm_create_root(snl_scene *s, int world, int W, int H, unsigned char bl
 	c->ranks.push_back(r0);
 	if(!r)
 		r = comm_rank_events(c->ranks[0]);
+	if(!r)
+		r = build_packet_list(c, c->ranks[0]);
 	if(!r)
 		r = comm_root_resources(c);
 	if(!r && blob) {
@@ -206,6 +248,8 @@ int snl_comm_attach(snl_scene *s, int rank, const unsigned char blob[SNL_COMM_BL
 	c->ranks.push_back(cr);
 	if(!r)
 		r = comm_rank_events(c->ranks[0]);
+	if(!r)
+		r = build_packet_list(c, c->ranks[0]);
 	if(r) {
 		snl_comm_destroy(c);
 		return r;
@@ -252,6 +296,8 @@ int snl_comm_create_local(snl_scene *const *scenes, int n, int W, int H, snl_com
 			}
 		}
 		r = comm_rank_events(c->ranks.back());
+		if(!r)
+			r = build_packet_list(c, c->ranks.back());
 	}
 	if(!r)
 		r = comm_root_resources(c);
@@ -277,21 +323,11 @@ void snl_comm_destroy(snl_comm *c) {
 			cudaEventDestroy(r.ev1);
 		if(r.ipc && r.seg)
 			cudaIpcCloseMemHandle(r.seg);
-		if(r.localReady)
-			cudaFree(r.localReady);
+		if(r.dPackets)
+			cudaFree(r.dPackets);
 	}
 	if(!c->ranks.empty() && c->ranks[0].rank == 0 && c->ranks[0].scene) {
 		cudaSetDevice(c->ranks[0].scene->device);
-		for(int b = 0; b < kCommBands; b++) {
-			if(c->copyStream[b]) {
-				cudaStreamSynchronize(c->copyStream[b]);
-				cudaStreamDestroy(c->copyStream[b]);
-			}
-			if(c->copyEv[b])
-				cudaEventDestroy(c->copyEv[b]);
-		}
-		if(c->openEv)
-			cudaEventDestroy(c->openEv);
 		if(c->hStats)
 			cudaFreeHost(c->hStats);
 		if(c->ownsSegment && c->ranks[0].seg)
@@ -326,8 +362,7 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 	SNL_REQUIRE(!bgr8_host || hostPitch >= (size_t)c->W * 3, SNL_ERR_INVALID, "host pitch too small");
 	const int W = c->W, H = c->H;
 	const unsigned seq = c->seq, slot = seq & 1u;
-	const int px = (W + 15) / 16, py = (H + 15) / 16;
-	const unsigned nPackets = (unsigned)(px * py);
+	const int py = (H + 15) / 16;
 	bool isRoot = false;
 	for(CommRank &r : c->ranks) {
 		snl_scene *s = r.scene;
@@ -352,42 +387,38 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 		if(r.rank == 0) {
 			isRoot = true;
 			SNL_CUDA(launch_frame_open(ctl, seq, c->world, s->stream));
-			SNL_CUDA(cudaEventRecord(c->openEv, s->stream));
-			s->launches++;
 		}
+		else  // the slot is open once rank 0 has read frame seq - 2 out of it and reset its counters
+			SNL_CUDA(launch_wait_counter(&ctl->ready[slot], seq + 1u, &ctl->error, s->stream));
+		s->launches++;
+		SNL_CUDA(cudaEventRecord(s->forkEv, s->stream));
 		const int variant = std::max(0, s->tune.choice);
-		// one CTA per packet this rank can take: its share plus a third (the ranks are alike: what varies is the cost of the
-		// packets they happen to draw), all of them when it renders alone. CTAs that find the frame handed out exit at once.
-		const int ctas = c->world == 1 ? (int)nPackets : (int)std::min<size_t>(nPackets, (size_t)nPackets * 4 / (3 * c->world) + 2 * s->smCount);
-		DynCtl d;
-		d.cursor = &ctl->cursor[slot];
-		d.bandDone = ctl->bandDone[slot];
-		d.ready = &ctl->ready[slot];
-		d.localReady = r.localReady + slot;
-		d.readyVal = seq + 1u;
-		d.nPackets = nPackets;
-		d.local = r.rank == 0 ? 1u : 0u;
-		d.rowsPerBand = (unsigned)c->rowsPerBand;
-		d.error = &ctl->error;
-		SNL_CUDA(launch_render(S, s->originPre.set(), g, W, H, nullptr, 0, frame, c->pitch, variant, s->stream, 0, -1, &d, ctas));
+		for(int b = 0; b < c->nBands; b++) {
+			cudaStream_t st = s->bandStream[b];
+			SNL_CUDA(cudaStreamWaitEvent(st, s->forkEv, 0));
+			const int first = r.bandFirst[b], count = r.bandFirst[b + 1] - first;
+			if(count > 0) {
+				SNL_CUDA(launch_render(S, s->originPre.set(), g, W, H, r.dPackets, r.bandFirst[kCommBands], frame, c->pitch, variant, st,
+									   first, count));
+				s->launches++;
+			}
+			SNL_CUDA(launch_band_signal(&ctl->bandDone[slot][b], st));
+			s->launches++;
+			if(r.rank == 0 && bgr8_host) {
+				const int r0 = b * c->rowsPerBand, r1 = std::min(py, (b + 1) * c->rowsPerBand);
+				const int y0 = r0 * 16, y1 = std::min(H, r1 * 16);
+				SNL_CUDA(launch_wait_counter(&ctl->bandDone[slot][b], (unsigned)c->world, &ctl->error, st));
+				s->launches++;
+				SNL_CUDA(cudaMemcpy2DAsync(bgr8_host + (size_t)y0 * hostPitch, hostPitch, frame + (size_t)y0 * c->pitch, c->pitch,
+										   (size_t)W * 3, y1 - y0, cudaMemcpyDeviceToHost, st));
+			}
+			SNL_CUDA(cudaEventRecord(s->bandEv[b], st));
+			SNL_CUDA(cudaStreamWaitEvent(s->stream, s->bandEv[b], 0));
+		}
 		SNL_CUDA(launch_frame_publish(ctl, s->dCounters.ptr, seq, r.rank, s->stream));
-		s->launches += 2;
+		s->launches++;
 		SNL_CUDA(cudaEventRecord(r.ev1, s->stream));
 		if(r.rank == 0) {
-			if(bgr8_host) {
-				for(int b = 0; b < c->nBands; b++) {
-					const int r0 = b * c->rowsPerBand, r1 = std::min(py, (b + 1) * c->rowsPerBand);
-					const int y0 = r0 * 16, y1 = std::min(H, r1 * 16);
-					cudaStream_t st = c->copyStream[b];
-					SNL_CUDA(cudaStreamWaitEvent(st, c->openEv, 0));
-					SNL_CUDA(launch_wait_counter(&ctl->bandDone[slot][b], (unsigned)((r1 - r0) * px), &ctl->error, st));
-					SNL_CUDA(cudaMemcpy2DAsync(bgr8_host + (size_t)y0 * hostPitch, hostPitch, frame + (size_t)y0 * c->pitch, c->pitch,
-											   (size_t)W * 3, y1 - y0, cudaMemcpyDeviceToHost, st));
-					SNL_CUDA(cudaEventRecord(c->copyEv[b], st));
-					SNL_CUDA(cudaStreamWaitEvent(s->stream, c->copyEv[b], 0));
-					s->launches++;
-				}
-			}
 			// every rank has published = every packet of the frame is stored and every counter is in
 			SNL_CUDA(launch_wait_counter(&ctl->statsArrived[slot], (unsigned)c->world, &ctl->error, s->stream));
 			s->launches++;

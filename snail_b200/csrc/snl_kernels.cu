@@ -266,39 +266,12 @@ __device__ __forceinline__ void store_tile(const unsigned char *tile, int px0, i
 	}
 }
 
-// DYN = false: one packet per CTA (blockIdx + firstPacket). DYN = true: persistent CTAs that fetch packet batches from
-// the frame's shared cursor and count every stored packet off in its row band (multi-GPU frame, snl_comm.cu); a separate
-// instantiation because the loop costs the static kernel registers (measured: +2 % frame time when folded into one).
-template <int FLAGS, bool SUPER, int MINB, bool DYN>
+template <int FLAGS, bool SUPER, int MINB>
 __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreSet pre, RayGenParams g, int W, int H,
 												 int packetsX, const int4 *__restrict__ packets,
-												 unsigned char *__restrict__ out, size_t pitch, int firstPacket, const DynCtl ctl) {
+												 unsigned char *__restrict__ out, size_t pitch, int firstPacket) {
 	__shared__ __align__(16) unsigned char tile[SUPER ? 16 : 16 * 48];
-	int packet = blockIdx.x + firstPacket;
-	if(DYN) {
-		// Multi-GPU frame: the CTA takes the next packet of the frame from the cursor all ranks share (system-scope atomic
-		// in rank 0's memory) instead of its block index, so the GPUs balance themselves packet by packet. Still one
-		// packet per CTA - a persistent loop costs the packet registers (+6 % per frame, measured) and coarser batches
-		// leave a tail (runs of 8 packets: +60 %); the other resident CTAs of the SM cover the fetch latency.
-		__shared__ unsigned sPacket;
-		if(threadIdx.x == 0) {
-			unsigned p = 0xffffffffu;
-			// the frame slot is opened by rank 0 (k_frame_open) once every rank has left the frame that used it before;
-			// the first CTA of this rank that sees it open leaves a note in local memory for the others
-			bool open = *(volatile unsigned *)ctl.localReady == ctl.readyVal;
-			if(!open && wait_sys<false>(ctl.ready, ctl.readyVal, ctl.error)) {
-				*(volatile unsigned *)ctl.localReady = ctl.readyVal;
-				open = true;
-			}
-			if(open)
-				p = atomicAdd_system(ctl.cursor, 1u);
-			sPacket = p < ctl.nPackets ? p : 0xffffffffu;
-		}
-		__syncthreads();
-		if(sPacket == 0xffffffffu)
-			return;  // the frame has been handed out (this rank launches a few CTAs more than its share)
-		packet = (int)sPacket;
-	}
+	const int packet = blockIdx.x + firstPacket;
 	PacketCounts pc = {};
 	TravCount tc = {0, 0, 0};
 	if(S.hasUber)
@@ -321,18 +294,6 @@ __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreS
 	flush_counts(S, pc, tc);  // its barriers also publish `tile`
 	if(!SUPER)
 		store_tile(tile, px0, py0, cw, ch, out, pitch);
-	if(DYN) {
-		__syncthreads();  // every pixel of the packet is on its way
-		if(threadIdx.x == 0) {
-			// release the packet to rank 0's copy streams: rank 0 itself only needs device scope (frame, counters and the
-			// waiting kernel all live on its GPU); a peer's stores cross NVLink and need the system-scope fence
-			if(ctl.local)
-				__threadfence();
-			else
-				__threadfence_system();
-			atomicAdd_system(ctl.bandDone + min((unsigned)(py0 >> 4) / ctl.rowsPerBand, (unsigned)kCommBands - 1u), 1u);
-		}
-	}
 }
 
 // ---- launch wrappers ------------------------------------------------------------------------------------------
@@ -395,59 +356,32 @@ cudaError_t launch_raytrace(const SceneDev &S, const PreSet &pre, const float *o
 }
 
 cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, const int4 *packets,
-						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st, int first, int count,
-						  const DynCtl *dyn, int persistentCtas) {
+						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st, int first, int count) {
 	const int px = (W + 15) / 16, py = (H + 15) / 16;
 	const int all = packets ? nPackets : px * py;
-	int grid = count < 0 ? all - first : count;
-	DynCtl ctl;
-	memset(&ctl, 0, sizeof(ctl));
-	if(dyn) {  // `persistentCtas` CTAs, each fetching one packet from dyn->cursor
-		ctl = *dyn;
-		grid = persistentCtas;
-		first = 0;
-	}
-	if(grid <= 0 || first < 0 || (!dyn && first + grid > all))
+	const int grid = count < 0 ? all - first : count;
+	if(grid <= 0 || first < 0 || first + grid > all)
 		return cudaSuccess;
 	const int MB = SNL_RENDER_MIN_BLOCKS;
-#define SNL_LAUNCH_RENDER(F, SUP, B, D) k_render<F, SUP, B, D><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first, ctl)
-	if(dyn) {  // full frames without supersampling only (snl_render_multi checks)
-		if(packets || S.gvSuper)
-			return cudaErrorInvalidValue;
-		if(S.instances)
-			SNL_LAUNCH_RENDER(2, false, MB, true);
-		else if(S.hasTransp)
-			SNL_LAUNCH_RENDER(1, false, MB, true);
-		else if(S.reflDepth2)
-			SNL_LAUNCH_RENDER(8, false, MB, true);
-		else if(variant == 1)
-			SNL_LAUNCH_RENDER(0, false, MB + 1, true);
-		else
-			SNL_LAUNCH_RENDER(0, false, MB, true);
-	}
-	else if(S.instances)  // Scene<DBVH>: simple shading only, so no transparency; supersampling is refused by the caller
-		SNL_LAUNCH_RENDER(2, false, MB, false);
+#define SNL_LAUNCH_RENDER(F, SUP, B) k_render<F, SUP, B><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first)
+	if(S.instances)  // Scene<DBVH>: simple shading only, so no transparency; supersampling is refused by the caller
+		SNL_LAUNCH_RENDER(2, false, MB);
 	else if(S.hasTransp) {
 		if(S.gvSuper)
-			SNL_LAUNCH_RENDER(1, true, MB, false);
+			SNL_LAUNCH_RENDER(1, true, MB);
 		else
-			SNL_LAUNCH_RENDER(1, false, MB, false);
+			SNL_LAUNCH_RENDER(1, false, MB);
 	}
 	else if(S.gvSuper)
-		SNL_LAUNCH_RENDER(0, true, MB, false);
+		SNL_LAUNCH_RENDER(0, true, MB);
 	else if(S.reflDepth2)
-		SNL_LAUNCH_RENDER(8, false, MB, false);
+		SNL_LAUNCH_RENDER(8, false, MB);
 	else if(variant == 1)
-		SNL_LAUNCH_RENDER(0, false, MB + 1, false);
+		SNL_LAUNCH_RENDER(0, false, MB + 1);
 	else
-		SNL_LAUNCH_RENDER(0, false, MB, false);
+		SNL_LAUNCH_RENDER(0, false, MB);
 #undef SNL_LAUNCH_RENDER
 	return cudaGetLastError();
-}
-
-int render_ctas_per_sm(const SceneDev &S, int variant) {
-	const int MB = SNL_RENDER_MIN_BLOCKS;
-	return (!S.instances && !S.hasTransp && !S.gvSuper && !S.reflDepth2 && variant == 1) ? MB + 1 : MB;
 }
 
 // ---- multi-GPU frame protocol (CommCtl in rank 0's memory, see snl_comm.cu) ------------------------------------
@@ -457,10 +391,8 @@ __global__ void k_frame_open(CommCtl *ctl, unsigned seq, int world) {
 	if((int)threadIdx.x < world && seq >= 2)
 		wait_sys<true>(&ctl->rankDone[threadIdx.x], seq - 1u, &ctl->error);
 	__syncwarp();
-	if(threadIdx.x == 0) {
-		ctl->cursor[slot] = 0u;
+	if(threadIdx.x == 0)
 		ctl->statsArrived[slot] = 0u;
-	}
 	if(threadIdx.x < kCounters)
 		ctl->stats[slot][threadIdx.x] = 0ull;
 	if(threadIdx.x < kCommBands)
@@ -491,12 +423,20 @@ __global__ void k_wait_counter(const unsigned *counter, unsigned expected, unsig
 	wait_sys<true>(counter, expected, error);
 }
 
+// Runs in-stream behind a rank's k_render of one row band: the kernel boundary has completed (and made visible) every
+// pixel store of that launch, peer stores included, so one system-scope increment tells rank 0 the band share is in.
+__global__ void k_band_signal(unsigned *counter) { atomicAdd_system(counter, 1u); }
+
 cudaError_t launch_frame_open(CommCtl *ctl, unsigned seq, int world, cudaStream_t st) {
 	k_frame_open<<<1, 32, 0, st>>>(ctl, seq, world);
 	return cudaGetLastError();
 }
 cudaError_t launch_frame_publish(CommCtl *ctl, const Counters *local, unsigned seq, int rank, cudaStream_t st) {
 	k_frame_publish<<<1, 32, 0, st>>>(ctl, local, seq, rank);
+	return cudaGetLastError();
+}
+cudaError_t launch_band_signal(unsigned *counter, cudaStream_t st) {
+	k_band_signal<<<1, 1, 0, st>>>(counter);
 	return cudaGetLastError();
 }
 cudaError_t launch_wait_counter(const unsigned *counter, unsigned expected, unsigned *error, cudaStream_t st) {

@@ -10,7 +10,6 @@ namespace snl {
 struct SceneDev;
 struct PreSet;
 struct WfBuffers;
-struct DynCtl;
 struct CommCtl;
 
 cudaError_t launch_pretransform(const GenTri *gtris, int nTris, const float origin[3], PreTri *out, cudaStream_t st);
@@ -27,16 +26,16 @@ cudaError_t launch_raytrace(const SceneDev &S, const PreSet &pre, const float *o
 // packets (count < 0: all of them).
 cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, const int4 *packets,
 						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st, int first = 0,
-						  int count = -1, const DynCtl *dyn = nullptr, int persistentCtas = 0);
-// resident CTAs per SM k_render's `variant` is compiled for (its grid as a persistent kernel = SMs x this)
-int render_ctas_per_sm(const SceneDev &S, int variant);
+						  int count = -1);
 
 // Multi-GPU frame protocol (snl_comm.cu; CommCtl lives in rank 0's memory):
 // rank 0, before its k_render: waits until every rank has finished frame seq - 2, clears slot seq & 1, opens it
 cudaError_t launch_frame_open(CommCtl *ctl, unsigned seq, int world, cudaStream_t st);
 // every rank, after its k_render: adds its ray counters to the frame's, marks the rank done with frame seq
 cudaError_t launch_frame_publish(CommCtl *ctl, const Counters *local, unsigned seq, int rank, cudaStream_t st);
-// rank 0: returns once *counter >= expected (all packets of a band stored / all ranks' counters in)
+// every rank, in-stream behind its k_render of a row band: one more rank's share of that band is stored
+cudaError_t launch_band_signal(unsigned *counter, cudaStream_t st);
+// rank 0 (and a peer waiting for a frame slot to open): returns once *counter >= expected (all packets of a band stored / all ranks' counters in)
 cudaError_t launch_wait_counter(const unsigned *counter, unsigned expected, unsigned *error, cudaStream_t st);
 
 // Farm tile format (src/render.cpp:140-166): frame tiles -> planar x, y - x, z - x byte planes at out + offsets[i].

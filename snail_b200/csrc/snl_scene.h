@@ -137,6 +137,7 @@ struct snl_scene {
 
 namespace snl {
 // host-side helpers shared by snl_capi.cu and snl_comm.cu
+int ensure_band_streams(snl_scene *s);
 int prepare_frame(snl_scene *s, const snl_camera *cam, int W, int H, int rank, SceneDev &S, RayGenParams &g);
 int render_local(snl_scene *s, const snl_camera *cam, int W, int H, const int *tiles, int nTiles, unsigned char *dOut,
 				  size_t pitch, int rank);

@@ -41,29 +41,14 @@ struct SceneDev {
 // peer access), all fields updated with system-scope atomics / release stores. Two frame slots alternate.
 enum { kCommBands = 8, kCommRanks = 16, kCommCtlBytes = 4096 };
 struct CommCtl {
-	unsigned cursor[2];                         // next packet of the frame in this slot
 	unsigned long long stats[2][kCounters];            // Counters of the frame summed over the ranks
-	unsigned bandDone[2][kCommBands];           // packets completed per row band
+	unsigned bandDone[2][kCommBands];           // ranks whose share of the row band is stored
 	unsigned ready[2];                          // seq + 1 once the slot has been opened for frame seq
 	unsigned statsArrived[2];
 	unsigned rankDone[kCommRanks];              // frames completed by each rank (seq + 1)
 	unsigned error;                             // a wait timed out somewhere
 };
 static_assert(sizeof(CommCtl) <= kCommCtlBytes, "CommCtl must fit its page");
-
-// Work source of k_render<DYN>: every CTA fetches its packet from the cursor the ranks share and reports it to its
-// band's counter when its pixels are stored.
-struct DynCtl {
-	unsigned *cursor;
-	unsigned *bandDone;     // [kCommBands] of this frame's slot
-	const unsigned *ready;  // fetch only once *ready == readyVal
-	unsigned *localReady;   // this rank's own copy of that observation (device-local)
-	unsigned readyVal;
-	unsigned nPackets;
-	unsigned rowsPerBand;   // packet rows per band
-	unsigned local;         // this rank owns the frame and the counters: device-scope release is enough
-	unsigned *error;
-};
 
 // Wavefront pipeline state for one frame (snl_wavefront.cu). NL = packets * 256 lanes; arrays are lane-indexed
 // (lane = packet * 256 + thread) unless noted, so the shading kernels keep the reference's packet / quad structure

@@ -161,7 +161,7 @@ def test_c_caller_renders_on_the_gpus_of_the_box(sb, tmp_path):
     subprocess.run(["gcc", "-std=c11", "-O1", "-Wall", "-I", os.path.join(ROOT, "include"),
                     os.path.join(ROOT, "tests", "c", "render_multi_test.c"), "-L", lib_dir, "-lsnail_b200", "-lm",
                     f"-Wl,-rpath,{lib_dir}", "-o", exe], check=True)
-    for ngpu in sorted({1, n}):
+    for ngpu in sorted({1, n}):  # one process, ngpu devices
         r = subprocess.run([exe, scene_path("lancia"), str(ngpu), "648", "360", "4"], capture_output=True, text=True, timeout=300)
         print(r.stdout)
         assert r.returncode == 0 and r.stdout.strip().endswith("PASS"), r.stdout + r.stderr
