@@ -364,7 +364,13 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 	const unsigned seq = c->seq, slot = seq & 1u;
 	const int py = (H + 15) / 16;
 	bool isRoot = false;
-	for(CommRank &r : c->ranks) {
+	// Phase 1, every local rank: whatever may allocate or synchronise (variant pick on the first frame, per-origin records).
+	// With several devices in ONE process this must be over before any device starts waiting on a peer: a cudaMalloc on
+	// one device updates its peers' mappings and would block behind their waiting kernels.
+	std::vector<SceneDev> devScene(c->ranks.size());
+	std::vector<RayGenParams> rayGen(c->ranks.size());
+	for(size_t i = 0; i < c->ranks.size(); i++) {
+		CommRank &r = c->ranks[i];
 		snl_scene *s = r.scene;
 		SNL_CUDA(cudaSetDevice(s->device));
 		SNL_REQUIRE(s->nGpuNodes > 0, SNL_ERR_STATE, "rank %d: no geometry", r.rank);
@@ -374,16 +380,23 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 			SNL_CUDA(s->dImage.reserve((size_t)W * 3 * H));
 			SNL_CUDA(cudaMemsetAsync(s->dCounters.ptr, 0, sizeof(Counters), s->stream));
 			SNL_TRY(render_local(s, cam, W, H, nullptr, 0, s->dImage.ptr, (size_t)W * 3, r.rank));
+			SNL_CUDA(cudaStreamSynchronize(s->stream));
 			s->tuneW = W;
 			s->tuneH = H;
 		}
-		CommCtl *ctl = reinterpret_cast<CommCtl *>(r.seg);
-		unsigned char *frame = r.seg + kCommCtlBytes + (size_t)slot * c->frameBytes;
 		SNL_CUDA(cudaMemsetAsync(s->dCounters.ptr, 0, sizeof(Counters), s->stream));
 		SNL_CUDA(cudaEventRecord(r.ev0, s->stream));
-		SceneDev S;
-		RayGenParams g;
-		SNL_TRY(prepare_frame(s, cam, W, H, r.rank, S, g));
+		SNL_TRY(prepare_frame(s, cam, W, H, r.rank, devScene[i], rayGen[i]));
+	}
+	// Phase 2: the frame itself, launches only.
+	for(size_t i = 0; i < c->ranks.size(); i++) {
+		CommRank &r = c->ranks[i];
+		snl_scene *s = r.scene;
+		const SceneDev &S = devScene[i];
+		const RayGenParams &g = rayGen[i];
+		SNL_CUDA(cudaSetDevice(s->device));
+		CommCtl *ctl = reinterpret_cast<CommCtl *>(r.seg);
+		unsigned char *frame = r.seg + kCommCtlBytes + (size_t)slot * c->frameBytes;
 		if(r.rank == 0) {
 			isRoot = true;
 			SNL_CUDA(launch_frame_open(ctl, seq, c->world, s->stream));
