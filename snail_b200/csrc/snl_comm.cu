@@ -58,7 +58,10 @@ struct CommRank {  // one rank driven by this process
 	int rank = 0;
 	unsigned char *seg = nullptr;  // rank 0's segment as this rank's device sees it
 	bool ipc = false;              // mapped with cudaIpcOpenMemHandle (else: owned, or a peer pointer of this process)
-	int4 *dPackets = nullptr;      // this rank's packets {x, y, w, h}, row bands in order
+	int4 *dPackets[2] = {nullptr, nullptr};  // this rank's packets {x, y, w, h}, row bands in order; [cur] is the live list
+	int cur = 0;
+	unsigned *dCost = nullptr;     // cycles every packet of the live list took in the last frame
+	int *dBandFirst = nullptr;     // device copy of bandFirst
 	int bandFirst[kCommBands + 1] = {};  // [b] .. [b + 1]: its packets of band b
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
 };
@@ -82,7 +85,8 @@ struct snl_comm {
 	bool ownsSegment = false;
 	// rank 0's side
 	int nBands = 1, rowsPerBand = 1;
-	unsigned long long *hStats = nullptr;  // pinned: kCounters counters + error word
+	bool sortByCost = true;  // next frame's packets of a band longest first (cycles measured this frame)
+	CommCtl *hCtl = nullptr;  // pinned copy of the control block (summed counters, error word)
 	float lastMs = 0.0f;
 };
 
@@ -97,8 +101,14 @@ int comm_geometry(snl_comm *c, int world, int W, int H) {
 	c->pitch = align_up((size_t)W * 3, 16);
 	c->frameBytes = align_up(c->pitch * H, 256);
 	c->segBytes = kCommCtlBytes + 2 * c->frameBytes;
-	const int py = (H + 15) / 16;
-	c->nBands = std::min<int>(kCommBands, py);
+	const int px = (W + 15) / 16, py = (H + 15) / 16;
+	// Row bands = launches per rank and frame (each band's rows go to the host while the next ones render). A band is
+	// worth its launches (~12 us of host time) only while a rank has well over a wave of packets per band: 1 band for a
+	// 1080p frame on 8 GPUs (1020 packets per rank), 8 for a 4K frame on 2.
+	c->nBands = std::max(1, std::min<int>(std::min<int>(kCommBands, py), px * py / world / 1000));
+	if(const char *e = getenv("SNL_COMM_BANDS"))
+		c->nBands = std::max(1, std::min<int>(std::min<int>(kCommBands, py), atoi(e)));
+	c->sortByCost = !(getenv("SNL_COMM_SORT") && getenv("SNL_COMM_SORT")[0] == '0');
 	c->rowsPerBand = (py + c->nBands - 1) / c->nBands;
 	c->nBands = (py + c->rowsPerBand - 1) / c->rowsPerBand;
 	return SNL_OK;
@@ -107,7 +117,7 @@ int comm_geometry(snl_comm *c, int world, int W, int H) {
 int comm_root_resources(snl_comm *c) {
 	CommRank &r0 = c->ranks[0];
 	SNL_CUDA(cudaSetDevice(r0.scene->device));
-	SNL_CUDA(cudaMallocHost(&c->hStats, 16 * sizeof(unsigned long long)));
+	SNL_CUDA(cudaMallocHost(&c->hCtl, sizeof(CommCtl)));
 	return SNL_OK;
 }
 
@@ -166,9 +176,15 @@ int build_packet_list(snl_comm *c, CommRank &r) {
 	for(int b = c->nBands; b <= kCommBands; b++)
 		r.bandFirst[b] = (int)list.size();
 	SNL_CUDA(cudaSetDevice(r.scene->device));
-	SNL_CUDA(cudaMalloc((void **)&r.dPackets, std::max<size_t>(list.size(), 1) * sizeof(int4)));
+	const size_t n = std::max<size_t>(list.size(), 1);
+	for(int k = 0; k < 2; k++)
+		SNL_CUDA(cudaMalloc((void **)&r.dPackets[k], n * sizeof(int4)));
+	SNL_CUDA(cudaMalloc((void **)&r.dCost, n * sizeof(unsigned)));
+	SNL_CUDA(cudaMalloc((void **)&r.dBandFirst, sizeof(r.bandFirst)));
+	SNL_CUDA(cudaMemset(r.dCost, 0, n * sizeof(unsigned)));
 	if(!list.empty())
-		SNL_CUDA(cudaMemcpy(r.dPackets, list.data(), list.size() * sizeof(int4), cudaMemcpyHostToDevice));
+		SNL_CUDA(cudaMemcpy(r.dPackets[0], list.data(), list.size() * sizeof(int4), cudaMemcpyHostToDevice));
+	SNL_CUDA(cudaMemcpy(r.dBandFirst, r.bandFirst, sizeof(r.bandFirst), cudaMemcpyHostToDevice));
 	return SNL_OK;
 }
 
@@ -323,13 +339,18 @@ void snl_comm_destroy(snl_comm *c) {
 			cudaEventDestroy(r.ev1);
 		if(r.ipc && r.seg)
 			cudaIpcCloseMemHandle(r.seg);
-		if(r.dPackets)
-			cudaFree(r.dPackets);
+		for(int4 *p : r.dPackets)
+			if(p)
+				cudaFree(p);
+		if(r.dCost)
+			cudaFree(r.dCost);
+		if(r.dBandFirst)
+			cudaFree(r.dBandFirst);
 	}
 	if(!c->ranks.empty() && c->ranks[0].rank == 0 && c->ranks[0].scene) {
 		cudaSetDevice(c->ranks[0].scene->device);
-		if(c->hStats)
-			cudaFreeHost(c->hStats);
+		if(c->hCtl)
+			cudaFreeHost(c->hCtl);
 		if(c->ownsSegment && c->ranks[0].seg)
 			cudaFree(c->ranks[0].seg);
 	}
@@ -404,29 +425,40 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 		else  // the slot is open once rank 0 has read frame seq - 2 out of it and reset its counters
 			SNL_CUDA(launch_wait_counter(&ctl->ready[slot], seq + 1u, &ctl->error, s->stream));
 		s->launches++;
-		SNL_CUDA(cudaEventRecord(s->forkEv, s->stream));
 		const int variant = std::max(0, s->tune.choice);
-		for(int b = 0; b < c->nBands; b++) {
-			cudaStream_t st = s->bandStream[b];
-			SNL_CUDA(cudaStreamWaitEvent(st, s->forkEv, 0));
-			const int first = r.bandFirst[b], count = r.bandFirst[b + 1] - first;
-			if(count > 0) {
-				SNL_CUDA(launch_render(S, s->originPre.set(), g, W, H, r.dPackets, r.bandFirst[kCommBands], frame, c->pitch, variant, st,
-									   first, count));
+		const int4 *list = r.dPackets[r.cur];
+		const int nList = r.bandFirst[kCommBands];
+		unsigned *cost = c->sortByCost ? r.dCost : nullptr;
+		if(c->nBands == 1) {
+			// one launch per rank; the frame is complete when every rank has published
+			if(nList > 0) {
+				SNL_CUDA(launch_render(S, s->originPre.set(), g, W, H, list, nList, frame, c->pitch, variant, s->stream, 0, nList, cost));
 				s->launches++;
 			}
-			SNL_CUDA(launch_band_signal(&ctl->bandDone[slot][b], st));
-			s->launches++;
-			if(r.rank == 0 && bgr8_host) {
-				const int r0 = b * c->rowsPerBand, r1 = std::min(py, (b + 1) * c->rowsPerBand);
-				const int y0 = r0 * 16, y1 = std::min(H, r1 * 16);
-				SNL_CUDA(launch_wait_counter(&ctl->bandDone[slot][b], (unsigned)c->world, &ctl->error, st));
+		}
+		else {
+			SNL_CUDA(cudaEventRecord(s->forkEv, s->stream));
+			for(int b = 0; b < c->nBands; b++) {
+				cudaStream_t st = s->bandStream[b];
+				SNL_CUDA(cudaStreamWaitEvent(st, s->forkEv, 0));
+				const int first = r.bandFirst[b], count = r.bandFirst[b + 1] - first;
+				if(count > 0) {
+					SNL_CUDA(launch_render(S, s->originPre.set(), g, W, H, list, nList, frame, c->pitch, variant, st, first, count, cost));
+					s->launches++;
+				}
+				SNL_CUDA(launch_band_signal(&ctl->bandDone[slot][b], st));
 				s->launches++;
-				SNL_CUDA(cudaMemcpy2DAsync(bgr8_host + (size_t)y0 * hostPitch, hostPitch, frame + (size_t)y0 * c->pitch, c->pitch,
-										   (size_t)W * 3, y1 - y0, cudaMemcpyDeviceToHost, st));
+				if(r.rank == 0 && bgr8_host) {
+					const int r0 = b * c->rowsPerBand, r1 = std::min(py, (b + 1) * c->rowsPerBand);
+					const int y0 = r0 * 16, y1 = std::min(H, r1 * 16);
+					SNL_CUDA(launch_wait_counter(&ctl->bandDone[slot][b], (unsigned)c->world, &ctl->error, st));
+					s->launches++;
+					SNL_CUDA(cudaMemcpy2DAsync(bgr8_host + (size_t)y0 * hostPitch, hostPitch, frame + (size_t)y0 * c->pitch, c->pitch,
+											   (size_t)W * 3, y1 - y0, cudaMemcpyDeviceToHost, st));
+				}
+				SNL_CUDA(cudaEventRecord(s->bandEv[b], st));
+				SNL_CUDA(cudaStreamWaitEvent(s->stream, s->bandEv[b], 0));
 			}
-			SNL_CUDA(cudaEventRecord(s->bandEv[b], st));
-			SNL_CUDA(cudaStreamWaitEvent(s->stream, s->bandEv[b], 0));
 		}
 		SNL_CUDA(launch_frame_publish(ctl, s->dCounters.ptr, seq, r.rank, s->stream));
 		s->launches++;
@@ -435,8 +467,15 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 			// every rank has published = every packet of the frame is stored and every counter is in
 			SNL_CUDA(launch_wait_counter(&ctl->statsArrived[slot], (unsigned)c->world, &ctl->error, s->stream));
 			s->launches++;
-			SNL_CUDA(cudaMemcpyAsync(c->hStats, ctl->stats[slot], sizeof(Counters), cudaMemcpyDeviceToHost, s->stream));
-			SNL_CUDA(cudaMemcpyAsync(c->hStats + kCounters, &ctl->error, sizeof(unsigned), cudaMemcpyDeviceToHost, s->stream));
+			if(c->nBands == 1 && bgr8_host)
+				SNL_CUDA(cudaMemcpy2DAsync(bgr8_host, hostPitch, frame, c->pitch, (size_t)W * 3, H, cudaMemcpyDeviceToHost, s->stream));
+			SNL_CUDA(cudaMemcpyAsync(c->hCtl, ctl, sizeof(CommCtl), cudaMemcpyDeviceToHost, s->stream));
+		}
+		if(cost && nList > 1) {
+			// off the frame's critical path: the list for the next frame, every band longest packet first
+			SNL_CUDA(launch_sort_band_packets(list, cost, r.dPackets[r.cur ^ 1], r.dBandFirst, c->nBands, s->stream));
+			s->launches++;
+			r.cur ^= 1;
 		}
 	}
 	c->seq++;
@@ -450,13 +489,13 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 	}
 	c->lastMs = ms;
 	if(isRoot)
-		SNL_REQUIRE(*(const unsigned *)(c->hStats + kCounters) == 0, SNL_ERR_STATE,
+		SNL_REQUIRE(c->hCtl->error == 0, SNL_ERR_STATE,
 					"snl_render_multi: a rank did not arrive within the time-out (every rank must call it once per frame)");
 	if(stats) {
 		memset(stats, 0, sizeof(*stats));
 		Counters k;
 		if(isRoot)
-			memcpy(&k, c->hStats, sizeof(k));  // summed over the ranks
+			memcpy(&k, c->hCtl->stats[slot], sizeof(k));  // summed over the ranks
 		else {                                   // this rank's share
 			snl_scene *s = c->ranks[0].scene;
 			SNL_CUDA(cudaMemcpy(&k, s->dCounters.ptr, sizeof(k), cudaMemcpyDeviceToHost));

@@ -269,9 +269,13 @@ __device__ __forceinline__ void store_tile(const unsigned char *tile, int px0, i
 template <int FLAGS, bool SUPER, int MINB>
 __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreSet pre, RayGenParams g, int W, int H,
 												 int packetsX, const int4 *__restrict__ packets,
-												 unsigned char *__restrict__ out, size_t pitch, int firstPacket) {
+												 unsigned char *__restrict__ out, size_t pitch, int firstPacket,
+												 unsigned *__restrict__ costOut) {
 	__shared__ __align__(16) unsigned char tile[SUPER ? 16 : 16 * 48];
+	__shared__ unsigned sStart;  // (shared, not a register: nothing extra stays live across the packet)
 	const int packet = blockIdx.x + firstPacket;
+	if(costOut && threadIdx.x == 0)
+		sStart = (unsigned)clock();
 	PacketCounts pc = {};
 	TravCount tc = {0, 0, 0};
 	if(S.hasUber)
@@ -294,6 +298,9 @@ __global__ void __launch_bounds__(kPacket, MINB) k_render(SceneDev S, const PreS
 	flush_counts(S, pc, tc);  // its barriers also publish `tile`
 	if(!SUPER)
 		store_tile(tile, px0, py0, cw, ch, out, pitch);
+	// cycles this packet kept its CTA slot (snl_render_multi orders next frame's packets by it, longest first)
+	if(costOut && threadIdx.x == 0)
+		costOut[packet] = max((unsigned)clock() - sStart, 1u);
 }
 
 // ---- launch wrappers ------------------------------------------------------------------------------------------
@@ -356,14 +363,15 @@ cudaError_t launch_raytrace(const SceneDev &S, const PreSet &pre, const float *o
 }
 
 cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, const int4 *packets,
-						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st, int first, int count) {
+						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st, int first, int count,
+						  unsigned *costOut) {
 	const int px = (W + 15) / 16, py = (H + 15) / 16;
 	const int all = packets ? nPackets : px * py;
 	const int grid = count < 0 ? all - first : count;
 	if(grid <= 0 || first < 0 || first + grid > all)
 		return cudaSuccess;
 	const int MB = SNL_RENDER_MIN_BLOCKS;
-#define SNL_LAUNCH_RENDER(F, SUP, B) k_render<F, SUP, B><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first)
+#define SNL_LAUNCH_RENDER(F, SUP, B) k_render<F, SUP, B><<<grid, kPacket, 0, st>>>(S, pre, g, W, H, px, packets, out, pitch, first, costOut)
 	if(S.instances)  // Scene<DBVH>: simple shading only, so no transparency; supersampling is refused by the caller
 		SNL_LAUNCH_RENDER(2, false, MB);
 	else if(S.hasTransp) {
@@ -423,6 +431,49 @@ __global__ void k_wait_counter(const unsigned *counter, unsigned expected, unsig
 	wait_sys<true>(counter, expected, error);
 }
 
+// One CTA per row band of a rank's packet list: the band's packets in descending order of the cycles they took in the
+// frame before (longest first = the tail of the band is made of its cheapest packets). Bitonic sort in shared memory;
+// bands of more than 4096 packets are passed through unchanged.
+__global__ void __launch_bounds__(1024) k_sort_band_packets(const int4 *__restrict__ in, const unsigned *__restrict__ cost,
+															 int4 *__restrict__ out, const int *__restrict__ bandFirst) {
+	__shared__ unsigned key[4096];
+	__shared__ unsigned short idx[4096];
+	const int first = bandFirst[blockIdx.x], n = bandFirst[blockIdx.x + 1] - first;
+	if(n > 4096 || n <= 1) {
+		for(int i = threadIdx.x; i < n; i += blockDim.x)
+			out[first + i] = in[first + i];
+		return;
+	}
+	int m = 2;
+	while(m < n)
+		m <<= 1;
+	for(int i = threadIdx.x; i < m; i += blockDim.x) {
+		key[i] = i < n ? cost[first + i] : 0u;  // recorded costs are >= 1: the padding sorts behind every packet
+		idx[i] = (unsigned short)i;
+	}
+	__syncthreads();
+	for(int k = 2; k <= m; k <<= 1)
+		for(int j = k >> 1; j > 0; j >>= 1) {
+			for(int i = threadIdx.x; i < m; i += blockDim.x) {
+				const int l = i ^ j;
+				if(l > i) {
+					const bool desc = (i & k) == 0;
+					const unsigned a = key[i], b = key[l];
+					if(desc ? a < b : a > b) {
+						key[i] = b;
+						key[l] = a;
+						const unsigned short t = idx[i];
+						idx[i] = idx[l];
+						idx[l] = t;
+					}
+				}
+			}
+			__syncthreads();
+		}
+	for(int i = threadIdx.x; i < n; i += blockDim.x)
+		out[first + i] = in[first + idx[i]];
+}
+
 // Runs in-stream behind a rank's k_render of one row band: the kernel boundary has completed (and made visible) every
 // pixel store of that launch, peer stores included, so one system-scope increment tells rank 0 the band share is in.
 __global__ void k_band_signal(unsigned *counter) { atomicAdd_system(counter, 1u); }
@@ -433,6 +484,11 @@ cudaError_t launch_frame_open(CommCtl *ctl, unsigned seq, int world, cudaStream_
 }
 cudaError_t launch_frame_publish(CommCtl *ctl, const Counters *local, unsigned seq, int rank, cudaStream_t st) {
 	k_frame_publish<<<1, 32, 0, st>>>(ctl, local, seq, rank);
+	return cudaGetLastError();
+}
+cudaError_t launch_sort_band_packets(const int4 *in, const unsigned *cost, int4 *out, const int *bandFirst, int nBands,
+									 cudaStream_t st) {
+	k_sort_band_packets<<<nBands, 1024, 0, st>>>(in, cost, out, bandFirst);
 	return cudaGetLastError();
 }
 cudaError_t launch_band_signal(unsigned *counter, cudaStream_t st) {

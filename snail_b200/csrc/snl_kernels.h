@@ -26,7 +26,10 @@ cudaError_t launch_raytrace(const SceneDev &S, const PreSet &pre, const float *o
 // packets (count < 0: all of them).
 cudaError_t launch_render(const SceneDev &S, const PreSet &pre, const RayGenParams &g, int W, int H, const int4 *packets,
 						  int nPackets, unsigned char *out, size_t pitch, int variant, cudaStream_t st, int first = 0,
-						  int count = -1);
+						  int count = -1, unsigned *costOut = nullptr);
+// snl_render_multi: every band [bandFirst[b], bandFirst[b + 1]) of a rank's packet list re-ordered by descending cost[]
+cudaError_t launch_sort_band_packets(const int4 *in, const unsigned *cost, int4 *out, const int *bandFirst, int nBands,
+									 cudaStream_t st);
 
 // Multi-GPU frame protocol (snl_comm.cu; CommCtl lives in rank 0's memory):
 // rank 0, before its k_render: waits until every rank has finished frame seq - 2, clears slot seq & 1, opens it
