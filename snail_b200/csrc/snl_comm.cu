@@ -64,6 +64,9 @@ struct CommRank {  // one rank driven by this process
 	int *dBandFirst = nullptr;     // device copy of bandFirst
 	int bandFirst[kCommBands + 1] = {};  // [b] .. [b + 1]: its packets of band b
 	cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+	cudaStream_t sortStream = nullptr;  // the next frame's packet order is worked out beside the caller's stream
+	cudaEvent_t sortIn = nullptr, sortOut = nullptr;
+	bool sortPending = false;
 };
 
 struct Blob {  // what travels from rank 0 to the other processes (any byte transport)
@@ -103,12 +106,15 @@ int comm_geometry(snl_comm *c, int world, int W, int H) {
 	c->segBytes = kCommCtlBytes + 2 * c->frameBytes;
 	const int px = (W + 15) / 16, py = (H + 15) / 16;
 	// Row bands = launches per rank and frame (each band's rows go to the host while the next ones render). A band is
-	// worth its launches (~12 us of host time) only while a rank has well over a wave of packets per band: 1 band for a
-	// 1080p frame on 8 GPUs (1020 packets per rank), 8 for a 4K frame on 2.
-	c->nBands = std::max(1, std::min<int>(std::min<int>(kCommBands, py), px * py / world / 1000));
+	// worth its launches (~10 us of host time) only while a rank has a good share of a wave of packets per band: 2 bands
+	// for a 1080p frame on 8 GPUs (1020 packets per rank), 8 for a 4K frame.
+	c->nBands = std::max(1, std::min<int>(std::min<int>(kCommBands, py), px * py / world / 500));
 	if(const char *e = getenv("SNL_COMM_BANDS"))
 		c->nBands = std::max(1, std::min<int>(std::min<int>(kCommBands, py), atoi(e)));
-	c->sortByCost = !(getenv("SNL_COMM_SORT") && getenv("SNL_COMM_SORT")[0] == '0');
+	// longest-packet-first pays where the tail of the frame matters: few packets per rank (and the list is short to sort)
+	c->sortByCost = px * py / world <= 2048;
+	if(const char *e = getenv("SNL_COMM_SORT"))
+		c->sortByCost = e[0] != '0';
 	c->rowsPerBand = (py + c->nBands - 1) / c->nBands;
 	c->nBands = (py + c->rowsPerBand - 1) / c->rowsPerBand;
 	return SNL_OK;
@@ -126,6 +132,9 @@ int comm_rank_events(CommRank &r) {
 
 	SNL_CUDA(cudaEventCreate(&r.ev0));
 	SNL_CUDA(cudaEventCreate(&r.ev1));
+	SNL_CUDA(cudaStreamCreateWithFlags(&r.sortStream, cudaStreamNonBlocking));
+	SNL_CUDA(cudaEventCreateWithFlags(&r.sortIn, cudaEventDisableTiming));
+	SNL_CUDA(cudaEventCreateWithFlags(&r.sortOut, cudaEventDisableTiming));
 	return ensure_band_streams(r.scene);
 }
 
@@ -337,6 +346,14 @@ void snl_comm_destroy(snl_comm *c) {
 			cudaEventDestroy(r.ev0);
 		if(r.ev1)
 			cudaEventDestroy(r.ev1);
+		if(r.sortStream) {
+			cudaStreamSynchronize(r.sortStream);
+			cudaStreamDestroy(r.sortStream);
+		}
+		if(r.sortIn)
+			cudaEventDestroy(r.sortIn);
+		if(r.sortOut)
+			cudaEventDestroy(r.sortOut);
 		if(r.ipc && r.seg)
 			cudaIpcCloseMemHandle(r.seg);
 		for(int4 *p : r.dPackets)
@@ -409,8 +426,11 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 		SNL_CUDA(cudaEventRecord(r.ev0, s->stream));
 		SNL_TRY(prepare_frame(s, cam, W, H, r.rank, devScene[i], rayGen[i]));
 	}
-	// Phase 2: the frame itself, launches only.
-	for(size_t i = 0; i < c->ranks.size(); i++) {
+	// Phase 2: the frame itself, launches only. Rank 0 goes LAST and its device->host copies last of all: a copy into
+	// pageable host memory blocks the calling thread until the stream gets there, and by then every other local rank
+	// must already be enqueued (they wait on the device for rank 0 to open the slot, not on the host).
+	for(size_t k = 0; k < c->ranks.size(); k++) {
+		const size_t i = (k + 1) % c->ranks.size();
 		CommRank &r = c->ranks[i];
 		snl_scene *s = r.scene;
 		const SceneDev &S = devScene[i];
@@ -426,6 +446,10 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 			SNL_CUDA(launch_wait_counter(&ctl->ready[slot], seq + 1u, &ctl->error, s->stream));
 		s->launches++;
 		const int variant = std::max(0, s->tune.choice);
+		if(r.sortPending) {  // this frame's packet order comes from the side stream
+			SNL_CUDA(cudaStreamWaitEvent(s->stream, r.sortOut, 0));
+			r.sortPending = false;
+		}
 		const int4 *list = r.dPackets[r.cur];
 		const int nList = r.bandFirst[kCommBands];
 		unsigned *cost = c->sortByCost ? r.dCost : nullptr;
@@ -448,6 +472,9 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 				}
 				SNL_CUDA(launch_band_signal(&ctl->bandDone[slot][b], st));
 				s->launches++;
+			}
+			for(int b = 0; b < c->nBands; b++) {
+				cudaStream_t st = s->bandStream[b];
 				if(r.rank == 0 && bgr8_host) {
 					const int r0 = b * c->rowsPerBand, r1 = std::min(py, (b + 1) * c->rowsPerBand);
 					const int y0 = r0 * 16, y1 = std::min(H, r1 * 16);
@@ -473,9 +500,13 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 		}
 		if(cost && nList > 1) {
 			// off the frame's critical path: the list for the next frame, every band longest packet first
-			SNL_CUDA(launch_sort_band_packets(list, cost, r.dPackets[r.cur ^ 1], r.dBandFirst, c->nBands, s->stream));
+			SNL_CUDA(cudaEventRecord(r.sortIn, s->stream));
+			SNL_CUDA(cudaStreamWaitEvent(r.sortStream, r.sortIn, 0));
+			SNL_CUDA(launch_sort_band_packets(list, cost, r.dPackets[r.cur ^ 1], r.dBandFirst, c->nBands, r.sortStream));
+			SNL_CUDA(cudaEventRecord(r.sortOut, r.sortStream));
 			s->launches++;
 			r.cur ^= 1;
+			r.sortPending = true;
 		}
 	}
 	c->seq++;
