@@ -422,8 +422,18 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 			s->tuneW = W;
 			s->tuneH = H;
 		}
-		SNL_CUDA(cudaMemsetAsync(s->dCounters.ptr, 0, sizeof(Counters), s->stream));
+		if(c->ranks.size() == 1) {
+			// one rank per process: open / wait for the frame slot first, so that the rank's device time (ev0 .. ev1: per-origin
+			// records, its packets, its publish) does not count the time it was early for the slot
+			CommCtl *ctl = reinterpret_cast<CommCtl *>(r.seg);
+			if(r.rank == 0)
+				SNL_CUDA(launch_frame_open(ctl, seq, c->world, s->stream));
+			else
+				SNL_CUDA(launch_wait_counter(&ctl->ready[slot], seq + 1u, &ctl->error, s->stream));
+			s->launches++;
+		}
 		SNL_CUDA(cudaEventRecord(r.ev0, s->stream));
+		SNL_CUDA(cudaMemsetAsync(s->dCounters.ptr, 0, sizeof(Counters), s->stream));
 		SNL_TRY(prepare_frame(s, cam, W, H, r.rank, devScene[i], rayGen[i]));
 	}
 	// Phase 2: the frame itself, launches only. Rank 0 goes LAST and its device->host copies last of all: a copy into
@@ -438,13 +448,14 @@ int snl_render_multi(snl_comm *c, const snl_camera *cam, unsigned char *bgr8_hos
 		SNL_CUDA(cudaSetDevice(s->device));
 		CommCtl *ctl = reinterpret_cast<CommCtl *>(r.seg);
 		unsigned char *frame = r.seg + kCommCtlBytes + (size_t)slot * c->frameBytes;
-		if(r.rank == 0) {
-			isRoot = true;
-			SNL_CUDA(launch_frame_open(ctl, seq, c->world, s->stream));
+		isRoot = isRoot || r.rank == 0;
+		if(c->ranks.size() > 1) {  // (a single local rank has done this in phase 1)
+			if(r.rank == 0)
+				SNL_CUDA(launch_frame_open(ctl, seq, c->world, s->stream));
+			else  // the slot is open once rank 0 has read frame seq - 2 out of it and reset its counters
+				SNL_CUDA(launch_wait_counter(&ctl->ready[slot], seq + 1u, &ctl->error, s->stream));
+			s->launches++;
 		}
-		else  // the slot is open once rank 0 has read frame seq - 2 out of it and reset its counters
-			SNL_CUDA(launch_wait_counter(&ctl->ready[slot], seq + 1u, &ctl->error, s->stream));
-		s->launches++;
 		const int variant = std::max(0, s->tune.choice);
 		if(r.sortPending) {  // this frame's packet order comes from the side stream
 			SNL_CUDA(cudaStreamWaitEvent(s->stream, r.sortOut, 0));
