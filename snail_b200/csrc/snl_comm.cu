@@ -111,8 +111,9 @@ int comm_geometry(snl_comm *c, int world, int W, int H) {
 	c->nBands = std::max(1, std::min<int>(std::min<int>(kCommBands, py), px * py / world / 500));
 	if(const char *e = getenv("SNL_COMM_BANDS"))
 		c->nBands = std::max(1, std::min<int>(std::min<int>(kCommBands, py), atoi(e)));
-	// longest-packet-first pays where the tail of the frame matters: few packets per rank (and the list is short to sort)
-	c->sortByCost = px * py / world <= 2048;
+	// longest-packet-first within every band (measured on sponza_like 1080p, 2 GPUs: 0.780 -> 0.758 ms per frame); the
+	// sorting kernel takes bands of up to 4096 packets
+	c->sortByCost = px * py / world / c->nBands <= 3500;
 	if(const char *e = getenv("SNL_COMM_SORT"))
 		c->sortByCost = e[0] != '0';
 	c->rowsPerBand = (py + c->nBands - 1) / c->nBands;
