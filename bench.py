@@ -287,6 +287,16 @@ def build_roofline(sb, args, w, W, H, sc, ms_per_launch, clocks, rank):
                              "after the timed region (counts and ratios only; launch_ms is the un-profiled CUDA-event time)"})
     else:
         rf.update({"achieved": None, "frac": None, "traffic": None, "counts_source": err})
+    # the roofline headline is the resource that binds: whichever of instruction issue and L1 wavefronts runs closer to
+    # its ceiling (both are reported); HBM and L2 are far from theirs for these L2-resident scenes
+    if n and rf.get("l1", {}).get("frac") and rf["l1"]["frac"] > rf["frac"]:
+        rf["issue"] = {"achieved": rf["achieved"], "peak": rf["peak"], "unit": rf["unit"], "frac": rf["frac"], "useful_frac": rf["useful_frac"]}
+        wps = rf["l1"]["wavefronts"] / t / 1e9
+        rf.update({"bound": "l1", "unit": "Gwavefront/s", "achieved": round(wps, 1), "frac": rf["l1"]["frac"],
+                   "peak": round(wps / rf["l1"]["frac"], 1),
+                   "peak_source": "one L1 (LSU data pipe) wavefront per SM and cycle: SMs x SM clock under load; coalesced loads reach "
+                                  f"{peaks['l1_gbs']:.0f} GB/s = {peaks['l1_gbs'] / (peaks['sms'] * sm_clk * 1e6 * 128 / 1e9):.2f} of it in "
+                                  "snl_measure_peaks (builder-measured)"})
     if wc:
         ab = 32 * wc["box_tests"] + 64 * wc["tri_tests"] + 16 * wc["rays"] + 64 * wc["shaded_hits"] + 3 * W * H
         rf["algorithmic"] = {"bytes_per_launch": int(ab), "gbs": round(ab / t / 1e9, 1), "box_tests": wc["box_tests"],

@@ -122,6 +122,20 @@ int snl_scene_set_geometry(snl_scene *, const void *nodes, int nNodes, const voi
 int snl_scene_build_device(snl_scene *, const void *tris, const void *shTris, int nTris, const int *triMatId,
 						   int nMatIds);
 float snl_scene_build_ms(snl_scene *);
+/* Which device builder snl_scene_build_device (and SNL_BUILD_DEVICE) runs:
+ *   SNL_BUILDER_LBVH  Morton-order linear BVH: ~0.4 ms for 268 K triangles, frames 13-25 % slower than on the SAH tree;
+ *   SNL_BUILDER_SAH   top-down 16-bin surface-area-heuristic build - the algorithm of the reference's BVH::FindSplit
+ *                     (src/bvh/tree.cpp:161-287: 16 bins per axis, costs traverse 0 / intersect 1, leaves of <= 4
+ *                     triangles) as a level-synchronous GPU build (snail_b200/csrc/snl_build_sah.cu): every level is a few
+ *                     flat kernels over triangles / nodes with integer min / max / add atomics, so the tree does not
+ *                     depend on scheduling and the same code runs as plain loops on the host (snl_host_build_binned_sah). */
+enum { SNL_BUILDER_LBVH = 0, SNL_BUILDER_SAH = 1 };
+int snl_scene_set_device_builder(snl_scene *, int builder);
+/* The binned-SAH build on the HOST (no device): tris = Triangle[nTris] (reference layout); gpuNodes receives up to
+ * max(nTris - 1, 1) 64-byte traversal nodes {child0 minx,maxx,miny,maxy | child1 ... | c0 minz,maxz,c1 minz,maxz | link0,
+ * link1, 0, 0} (link >= 0: node index, < 0: ~(first | (count - 1) << 26) into the re-ordered triangles), order[i] = index
+ * of the input triangle that becomes triangle i. */
+int snl_host_build_binned_sah(const void *tris, int nTris, void *gpuNodes, int *nNodes, int *order, int *height);
 
 /* Instanced two-level BVH: Scene<DBVH> over ObjectInstances of this scene's BVH (src/dbvh/tree.h, the `-instances n`
  * mode of src/rtracer.cpp:146-178,359-363). snl_instance = the data members of ObjectInstance (:177-178): rotation rows
@@ -176,6 +190,7 @@ int snl_set_reflection_depth(snl_scene *, int depth);
  * buildFlags: 1 noShadingData, 2 fastBuild, 4 useSah; ours: 8 = SNL_BUILD_DEVICE, the host only parses the file and
  * the tree is built on the GPU, see snl_scene_build_device). mtlPath/texDir may be NULL. */
 #define SNL_BUILD_DEVICE 8
+#define SNL_BUILD_SAH_BINNED 16 /* with SNL_BUILD_DEVICE: the binned-SAH device builder instead of the LBVH */
 int snl_scene_load_obj(snl_scene *, const char *objPath, const char *mtlPath, const char *texDir,
 					   int flipNormalsFlag, int buildFlags);
 

@@ -22,7 +22,7 @@ ABI_SYMBOLS = [
     "snl_trace_rays", "snl_trace_shadow", "snl_raytrace", "snl_render", "snl_render_dev", "snl_render_farm", "snl_scene_sync",
     "snl_scene_launch_count", "snl_scene_render_variant", "snl_scene_stream", "snl_host_scene_load_obj", "snl_host_scene_free",
     "snl_host_scene_counts", "snl_host_scene_copy", "snl_host_scene_material", "snl_host_scene_texture",
-    "snl_scene_set_host_scene", "snl_scene_build_device", "snl_scene_build_ms", "snl_scene_set_instances",
+    "snl_scene_set_host_scene", "snl_scene_build_device", "snl_scene_build_ms", "snl_scene_set_device_builder", "snl_host_build_binned_sah", "snl_scene_set_instances",
     "snl_trace_primary_inst", "snl_scene_copy_dbvh", "snl_host_dbvh_build", "snl_frame_create", "snl_frame_open", "snl_frame_close", "snl_frame_read",
     "snl_measure_peaks", "snl_comm_create_root", "snl_comm_attach", "snl_comm_create_local", "snl_comm_info", "snl_render_multi",
     "snl_comm_frame", "snl_comm_destroy",
@@ -36,6 +36,9 @@ SHTRI_DTYPE = np.dtype([("uv", "<f4", (3, 2)), ("nrm", "<f4", (3, 3)), ("mat", "
 
 NO_SHADING_DATA, FAST_BUILD, USE_SAH = 1, 2, 4
 BUILD_DEVICE = 8  # ours: tree built on the GPU (snl_scene_build_device)
+BUILD_SAH_BINNED = 16  # with BUILD_DEVICE: the binned-SAH device builder instead of the LBVH
+BUILDER_LBVH, BUILDER_SAH = 0, 1
+GPUNODE_DTYPE = np.dtype([("b0", "<f4", 4), ("b1", "<f4", 4), ("bz", "<f4", 4), ("link", "<i4", 4)])
 MAT_SIMPLE, MAT_UBER, MAT_TEX, MAT_TRANSPARENT = 0, 1, 2, 3
 
 
@@ -125,6 +128,8 @@ def load_library(counters: bool = False) -> C.CDLL:
     L.snl_scene_copy_dbvh.argtypes = [vp, ip, vp, ip, vp, vp]
     L.snl_host_dbvh_build.argtypes = [vp, i, vp, vp, vp, ip, vp, vp]
     L.snl_scene_build_device.argtypes = [vp, vp, vp, i, vp, i]
+    L.snl_scene_set_device_builder.argtypes = [vp, i]
+    L.snl_host_build_binned_sah.argtypes = [vp, i, vp, ip, vp, ip]
     L.snl_scene_build_ms.argtypes = [vp]
     L.snl_scene_build_ms.restype = C.c_float
     L.snl_scene_set_materials.argtypes = [vp, vp, i, vp, i]
@@ -186,6 +191,21 @@ def measure_peaks(device: int = 0) -> dict:
     if r:
         raise SnlError(r, L.snl_last_error().decode())
     return {n: getattr(p, n) for n, _ in p._fields_}
+
+
+def host_build_binned_sah(tris):
+    """The binned-SAH builder of snl_build_sah.cu run on the host: (64-byte traversal nodes, triangle order, height)."""
+    L = load_library()
+    tris = np.ascontiguousarray(tris)
+    assert tris.dtype.itemsize == 64
+    n = len(tris)
+    nodes = np.zeros(max(n - 1, 1), GPUNODE_DTYPE)
+    order = np.zeros(n, np.int32)
+    nn, h = C.c_int(), C.c_int()
+    r = L.snl_host_build_binned_sah(_ptr(tris), n, _ptr(nodes), C.byref(nn), _ptr(order), C.byref(h))
+    if r:
+        raise SnlError(r, L.snl_last_error().decode())
+    return nodes[: nn.value], order, h.value
 
 
 def host_dbvh_build(instances, tree_min, tree_max):
@@ -308,6 +328,10 @@ class Scene:
         matids = np.ascontiguousarray(matids if matids is not None else [], np.int32)
         self._check(self.L.snl_scene_build_device(self.h, _ptr(tris), _ptr(shtris), len(tris),
                                                   _ptr(matids) if len(matids) else None, len(matids)))
+
+    def set_device_builder(self, builder: int):
+        """BUILDER_LBVH (fast) or BUILDER_SAH (binned SAH, the reference's tree quality) for build_device / BUILD_DEVICE."""
+        self._check(self.L.snl_scene_set_device_builder(self.h, builder))
 
     def set_instances(self, instances):
         """instances: (n, 12) float32 = ObjectInstance {rotation rows (9), translation (3)}; n = 0: plain BVH again."""

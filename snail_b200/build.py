@@ -14,7 +14,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libsnail_b200.so")
 LIB_COUNTERS = os.path.join(HERE, "libsnail_b200_counters.so")
 
-SOURCES = ["snl_kernels.cu", "snl_wavefront.cu", "snl_build.cu", "snl_capi.cu", "snl_comm.cu", "snl_peaks.cu", "snl_host_scene.cpp", "snl_host_dbvh.cpp"]
+SOURCES = ["snl_kernels.cu", "snl_wavefront.cu", "snl_build.cu", "snl_build_sah.cu", "snl_capi.cu", "snl_comm.cu", "snl_peaks.cu", "snl_host_scene.cpp", "snl_host_dbvh.cpp"]
 HEADERS = ["snl_device.cuh", "snl_kernels.h", "snl_scene.h", "snl_scene_dev.h", "snl_types.h", "snl_host_scene.h",
            os.path.join("..", "..", "include", "snail_b200.h")]
 

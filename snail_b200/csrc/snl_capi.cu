@@ -490,10 +490,14 @@ static int build_geometry_on_device(snl_scene *s) {
 	}
 	SNL_CUDA(s->dTris.reserve(nTris));
 	SNL_CUDA(s->dNodes.reserve(std::max(nTris - 1, 1)));
-	int height = 0, launches = 0;
-	cudaError_t err = device_build_lbvh(inTris.ptr, s->hasShading ? inSh.ptr : nullptr, nTris, s->dTris.ptr,
-										s->hasShading ? s->dShTris.ptr : nullptr, s->dNodes.ptr, &height, s->devBBox, s->stream,
-										&launches, &s->buildMs);
+	int height = 0, launches = 0, nNodes = std::max(nTris - 1, 1);
+	cudaError_t err = s->deviceBuilder == SNL_BUILDER_SAH
+						  ? device_build_sah(inTris.ptr, s->hasShading ? inSh.ptr : nullptr, nTris, s->dTris.ptr,
+											 s->hasShading ? s->dShTris.ptr : nullptr, s->dNodes.ptr, &nNodes, &height, s->devBBox, s->stream,
+											 &launches, &s->buildMs)
+						  : device_build_lbvh(inTris.ptr, s->hasShading ? inSh.ptr : nullptr, nTris, s->dTris.ptr,
+											  s->hasShading ? s->dShTris.ptr : nullptr, s->dNodes.ptr, &height, s->devBBox, s->stream,
+											  &launches, &s->buildMs);
 	inTris.release();
 	inSh.release();
 	if(err != cudaSuccess) {
@@ -508,7 +512,7 @@ static int build_geometry_on_device(snl_scene *s) {
 	if(s->nTriMat)
 		SNL_CUDA(cudaMemcpy(s->dTriMat.ptr, h.triMatId.data(), s->nTriMat * sizeof(int), cudaMemcpyHostToDevice));
 	s->nTris = nTris;
-	s->nGpuNodes = std::max(nTris - 1, 1);
+	s->nGpuNodes = nNodes;
 	s->gpuDepth = height;
 	s->devBuilt = true;
 	for(auto &e : s->lightPre)
@@ -602,6 +606,29 @@ int snl_scene_build_device(snl_scene *s, const void *tris, const void *shTris, i
 }
 
 float snl_scene_build_ms(snl_scene *s) { return s ? s->buildMs : 0.0f; }
+
+int snl_scene_set_device_builder(snl_scene *s, int builder) {
+	SNL_REQUIRE(s, SNL_ERR_INVALID, "null scene");
+	SNL_REQUIRE(builder == SNL_BUILDER_LBVH || builder == SNL_BUILDER_SAH, SNL_ERR_INVALID, "unknown builder %d", builder);
+	s->deviceBuilder = builder;
+	return SNL_OK;
+}
+
+int snl_host_build_binned_sah(const void *tris, int nTris, void *gpuNodes, int *nNodes, int *order, int *height) {
+	SNL_REQUIRE(tris && nTris > 0 && gpuNodes && nNodes && order && height, SNL_ERR_INVALID, "bad argument");
+	HostBVH h;
+	h.tris.assign((const RefTriangle *)tris, (const RefTriangle *)tris + nTris);
+	const std::vector<GenTri> gt = gen_tris(h);
+	std::vector<GpuNode> nodes;
+	std::vector<unsigned> ord;
+	const int r = host_build_binned_sah(gt.data(), nTris, nodes, ord, height);
+	SNL_REQUIRE(r > 0, SNL_ERR_UNSUPPORTED, "binned SAH build failed (%d: -2 node capacity, -3 deeper than the traversal stack)", r);
+	*nNodes = r;
+	memcpy(gpuNodes, nodes.data(), (size_t)r * sizeof(GpuNode));
+	for(int i = 0; i < nTris; i++)
+		order[i] = (int)ord[i];
+	return SNL_OK;
+}
 
 int snl_scene_set_instances(snl_scene *s, const snl_instance *inst, int n) {
 	SNL_REQUIRE(s && n >= 0 && (n == 0 || inst), SNL_ERR_INVALID, "bad argument");
@@ -1383,10 +1410,12 @@ int snl_scene_load_obj(snl_scene *s, const char *objPath, const char *mtlPath, c
 	SNL_REQUIRE(s && objPath, SNL_ERR_INVALID, "null argument");
 	HostScene hs;
 	std::string err;
-	if(!load_obj_scene(objPath, mtlPath, texDir, flipNormalsFlag, buildFlags, hs, err)) {
+	if(!load_obj_scene(objPath, mtlPath, texDir, flipNormalsFlag, buildFlags & ~SNL_BUILD_SAH_BINNED, hs, err)) {
 		set_error("%s", err.c_str());
 		return SNL_ERR_IO;
 	}
+	if(buildFlags & SNL_BUILD_DEVICE)
+		s->deviceBuilder = (buildFlags & SNL_BUILD_SAH_BINNED) ? SNL_BUILDER_SAH : SNL_BUILDER_LBVH;
 	return set_host_scene(s, hs);
 }
 

@@ -57,4 +57,10 @@ cudaError_t device_build_lbvh(const GenTri *inTris, const RefShTri *inSh, int n,
 							  GpuNode *outNodes, int *heightOut, float bboxOut[6], cudaStream_t st, int *launches,
 							  float *kernelMs);
 
+// Device-side binned-SAH build (snl_build_sah.cu): same outputs as device_build_lbvh plus the number of GpuNode records
+// written (<= n - 1). Synchronises the stream once per tree level.
+cudaError_t device_build_sah(const GenTri *inTris, const RefShTri *inSh, int n, GenTri *outTris, RefShTri *outSh,
+							 GpuNode *outNodes, int *nNodesOut, int *heightOut, float bboxOut[6], cudaStream_t st, int *launches,
+							 float *kernelMs);
+
 }  // namespace snl

@@ -84,6 +84,7 @@ struct snl_scene {
 	bool devBuilt = false;     // tree built by snl_build.cu (host.nodes is empty)
 	float devBBox[6] = {0};    // its scene box
 	float buildMs = 0.0f;      // device time of the last device build
+	int deviceBuilder = 0;     // SNL_BUILDER_LBVH / SNL_BUILDER_SAH: which device builder a soup goes through
 
 	// instanced form (DBVH over ObjectInstances of this scene's BVH, snl_scene_set_instances); empty = plain BVH
 	std::vector<snl::HostInstance> instances;  // in DBVH::elements order
@@ -138,6 +139,8 @@ struct snl_scene {
 namespace snl {
 // host-side helpers shared by snl_capi.cu and snl_comm.cu
 int ensure_band_streams(snl_scene *s);
+// the binned-SAH builder of snl_build_sah.cu run as plain loops on the host; returns the number of GpuNode records
+int host_build_binned_sah(const GenTri *inTris, int n, std::vector<GpuNode> &nodes, std::vector<unsigned> &orderOut, int *heightOut);
 int prepare_frame(snl_scene *s, const snl_camera *cam, int W, int H, int rank, SceneDev &S, RayGenParams &g);
 int render_local(snl_scene *s, const snl_camera *cam, int W, int H, const int *tiles, int nTiles, unsigned char *dOut,
 				  size_t pitch, int rank);

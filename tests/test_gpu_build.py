@@ -1,7 +1,9 @@
-"""Device-side BVH build (snail_b200/csrc/snl_build.cu) against the committed goldens, which are
-outputs of the reference on ITS tree. The device builder makes a different tree (Morton-order LBVH), so triangle ids
-are not comparable, but the nearest hit is a property of the triangles alone: t and the barycentrics must come out
-bit-identical wherever the reference's hit is unambiguous, and every rendered stage must match the golden frames."""
+"""Device-side BVH builds against the committed goldens, which are outputs of the reference on
+ITS tree: the Morton-order LBVH (snail_b200/csrc/snl_build.cu) and the level-synchronous binned-SAH build
+(snl_build_sah.cu, the reference's 16-bin FindSplit as flat GPU kernels). Either makes a different tree from the
+reference's, so triangle ids are not comparable, but the nearest hit is a property of the triangles alone: t and the
+barycentrics must come out bit-identical wherever the reference's hit is unambiguous, and every rendered stage must
+match the golden frames. The binned-SAH tree must also be THE tree its host run builds (tests/test_build_sah_cpu.py)."""
 import json
 import os
 
@@ -38,9 +40,13 @@ def load(sb, name, flags):
     return c, g, sc
 
 
+BUILDERS = {"lbvh": 0, "sah": 16}  # + sb.BUILD_DEVICE; 16 = sb.BUILD_SAH_BINNED
+
+
+@pytest.mark.parametrize("builder", list(BUILDERS))
 @pytest.mark.parametrize("name", list(MANIFEST["cases"]))
-def test_device_built_tree_gives_the_reference_hits(sb, name):
-    c, g, sc = load(sb, name, sb.BUILD_DEVICE)
+def test_device_built_tree_gives_the_reference_hits(sb, name, builder):
+    c, g, sc = load(sb, name, sb.BUILD_DEVICE | BUILDERS[builder])
     W, H = int(g["size"][0]), int(g["size"][1])
     cam = sb.Camera.from_array(g["camera"])
     tri, t, bary = sc.trace_primary(cam, W, H)
@@ -48,7 +54,7 @@ def test_device_built_tree_gives_the_reference_hits(sb, name):
     assert (hit_g != hit).sum() <= max(2, 1e-3 * W * H)  # silhouette pixels only
     both = hit_g & hit
     same_t = t[both] == g["t"][both]
-    print(f"{name}: build {sc.build_ms():.3f} ms for {c['n_tris']} tris, depth {sc.counts()['depth']}, "
+    print(f"{name}/{builder}: build {sc.build_ms():.3f} ms for {c['n_tris']} tris, depth {sc.counts()['depth']}, "
           f"t bit-identical on {same_t.mean()*100:.4f}% of {both.sum()} hits")
     assert float(same_t.mean()) >= 0.999  # the rest: t ties between two triangles resolved the other way
     assert (np.abs(t[both] - g["t"][both]) <= 1e-5 * np.abs(g["t"][both])).mean() >= 0.9999
@@ -58,9 +64,10 @@ def test_device_built_tree_gives_the_reference_hits(sb, name):
     sc.close()
 
 
+@pytest.mark.parametrize("builder", list(BUILDERS))
 @pytest.mark.parametrize("name", list(MANIFEST["cases"]))
-def test_device_built_tree_renders_the_golden_frames(sb, name):
-    c, g, sc = load(sb, name, sb.BUILD_DEVICE)
+def test_device_built_tree_renders_the_golden_frames(sb, name, builder):
+    c, g, sc = load(sb, name, sb.BUILD_DEVICE | BUILDERS[builder])
     W, H = int(g["size"][0]), int(g["size"][1])
     cam = sb.Camera.from_array(g["camera"])
     lg = g["light"]
@@ -74,7 +81,7 @@ def test_device_built_tree_renders_the_golden_frames(sb, name):
         if stage != "depth":
             err[undef] = 0
         frac = float((err <= 1).mean())
-        print(f"{name}/{stage}: within 1/255 on {frac*100:.3f}%")
+        print(f"{name}/{builder}/{stage}: within 1/255 on {frac*100:.3f}%")
         assert frac >= 0.999, stage
     sc.close()
 
@@ -94,12 +101,14 @@ def make_tris(sb, verts):
     return out
 
 
+@pytest.mark.parametrize("builder", [0, 1])
 @pytest.mark.parametrize("count", [1, 2, 3, 5, 33, 300])
-def test_soup_edge_cases(sb, count):
+def test_soup_edge_cases(sb, count, builder):
     """1 triangle (no inner node), tiny counts around the leaf rule, and `count` copies of ONE triangle (all Morton keys
     equal: the index tie-break decides the hierarchy; > 32 copies cannot collapse into a single leaf)."""
     tri = [[-1, -1, 5], [1, -1, 5], [0, 1, 5]]
     sc = sb.Scene(0)
+    sc.set_device_builder(builder)
     sc.build_device(make_tris(sb, [tri] * count))
     o = np.zeros((4, 3), np.float32)
     d = np.float32([[0, 0, 1], [0.05, -0.1, 1], [0, 0, -1], [3, 0, 1]])
@@ -110,7 +119,8 @@ def test_soup_edge_cases(sb, count):
     sc.close()
 
 
-def test_soup_order_does_not_matter(sb):
+@pytest.mark.parametrize("builder", [0, 1])
+def test_soup_order_does_not_matter(sb, builder):
     """The same triangles shuffled give the same hits (t, u, v) - the builder sorts them itself."""
     rng = np.random.default_rng(3)
     c = rng.random((2000, 1, 3)).astype(np.float32) * 10
@@ -122,8 +132,9 @@ def test_soup_order_does_not_matter(sb):
     res = []
     for perm in (np.arange(2000), rng.permutation(2000)):
         sc = sb.Scene(0)
+        sc.set_device_builder(builder)
         sc.build_device(tris[perm])
-        ids, t, bary = sc.trace_rays(o, d)  # ids are positions in the builder's own (Morton) order: not compared
+        ids, t, bary = sc.trace_rays(o, d)  # ids are positions in the builder's own order: not compared
         res.append((ids >= 0, t, bary))
         sc.close()
     assert (res[0][0] == res[1][0]).all()
@@ -133,6 +144,29 @@ def test_soup_order_does_not_matter(sb):
     assert res[0][0].mean() > 0.3  # the test does hit things
 
 
+def test_device_sah_tree_is_the_tree_of_its_host_run(sb):
+    """Integer min / max / add atomics only: the device build cannot depend on scheduling, so it must reproduce the host
+    run of the same functors. Checked through what the ABI exposes: the triangle a primary ray hits, mapped back to the
+    input order, is the same triangle (device ids index the device's order, host ids the host run's)."""
+    c, g, sc = load(sb, "lancia", sb.USE_SAH)
+    _, tris, _, _ = sc.host_bvh()
+    sc.close()
+    nodes, order, height = sb.host_build_binned_sah(tris)
+    dev = sb.Scene(0)
+    dev.set_device_builder(sb.BUILDER_SAH)
+    dev.build_device(tris)
+    assert dev.counts()["depth"] == height and dev.counts()["nodes"] == len(nodes)
+    W, H = int(g["size"][0]), int(g["size"][1])
+    tri, t, _ = dev.trace_primary(sb.Camera.from_array(g["camera"]), W, H)
+    hit = (tri >= 0) & (g["tri"] >= 0)
+    # golden ids index the reference order = `tris`; order[i] = input index of the triangle at position i of the built tree
+    same = order[np.maximum(tri, 0)] == g["tri"]
+    print(f"lancia: device binned-SAH build {dev.build_ms():.3f} ms, {len(nodes)} inner nodes, height {height}; same triangle as the "
+          f"golden on {same[hit].mean()*100:.4f} % of the hits")
+    assert float(same[hit].mean()) >= 0.999
+    dev.close()
+
+
 def test_device_build_equals_host_build_on_the_bench_scene(sb):
     from snail_b200 import workloads
     try:
@@ -140,8 +174,8 @@ def test_device_build_equals_host_build_on_the_bench_scene(sb):
     except FileNotFoundError as e:
         pytest.skip(str(e))
     W, H = 640, 360
-    imgs, ms = [], []
-    for flags in (sb.USE_SAH, sb.BUILD_DEVICE):
+    imgs, ms, names = [], [], []
+    for label, flags in (("host SAH sweep", sb.USE_SAH), ("device LBVH", sb.BUILD_DEVICE), ("device binned SAH", sb.BUILD_DEVICE | sb.BUILD_SAH_BINNED)):
         sc = sb.Scene(0)
         sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"], build_flags=flags)
         cam, light = sb.bench_camera(*sc.bbox(), inside=True)
@@ -151,9 +185,11 @@ def test_device_build_equals_host_build_on_the_bench_scene(sb):
         img, st = sc.render(cam, W, H)
         imgs.append(img)
         ms.append(st["kernel_ms"])
-        if flags == sb.BUILD_DEVICE:
-            print(f"sponza_like: device build {sc.build_ms():.3f} ms, depth {sc.counts()['depth']}")
+        names.append(label)
+        if flags & sb.BUILD_DEVICE:
+            print(f"sponza_like: {label}: build {sc.build_ms():.3f} ms, depth {sc.counts()['depth']}")
         sc.close()
-    err = np.abs(imgs[0].astype(np.int16) - imgs[1].astype(np.int16)).max(axis=2)
-    print(f"frame {W}x{H}: host tree {ms[0]:.3f} ms, device tree {ms[1]:.3f} ms; equal within 1/255 on {(err <= 1).mean()*100:.3f}%")
-    assert float((err <= 1).mean()) >= 0.999
+    for k in (1, 2):
+        err = np.abs(imgs[0].astype(np.int16) - imgs[k].astype(np.int16)).max(axis=2)
+        print(f"frame {W}x{H}: {names[0]} {ms[0]:.3f} ms, {names[k]} {ms[k]:.3f} ms; equal within 1/255 on {(err <= 1).mean()*100:.3f}%")
+        assert float((err <= 1).mean()) >= 0.999

@@ -15,7 +15,7 @@ W, H = 1920, 1080
 for name in sys.argv[1:] or ["sponza_like_whitted", "feline_whitted", "barracks_whitted"]:
     w = workloads.resolve(name)
     row = {"workload": name}
-    for label, flags in (("host_sah", sb.USE_SAH), ("device_lbvh", sb.BUILD_DEVICE)):
+    for label, flags in (("host_sah", sb.USE_SAH), ("device_lbvh", sb.BUILD_DEVICE), ("device_binned_sah", sb.BUILD_DEVICE | sb.BUILD_SAH_BINNED)):
         sc = sb.Scene(0)
         t0 = time.perf_counter()
         sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"], build_flags=flags)
@@ -38,4 +38,6 @@ for name in sys.argv[1:] or ["sponza_like_whitted", "feline_whitted", "barracks_
     # HBM traffic of the build as accounted in snl_build.cu's header (bytes per triangle, sort = 8 passes r+w of 12 B)
     bytes_per_tri = 96 + 44 + 8 * 24 + 320 + 200
     t["algorithmic_GBps"] = round(bytes_per_tri * t["tris"] / (t["device_build_ms"] * 1e-3) / 1e9, 1) if t["device_build_ms"] else None
+    for k in ("device_lbvh", "device_binned_sah"):
+        row[k]["render_vs_host_tree"] = round(row[k]["render_ms"] / row["host_sah"]["render_ms"], 4)
     print(json.dumps(row), flush=True)
