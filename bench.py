@@ -40,6 +40,8 @@ def parse_args():
     ap.add_argument("--compose", default="p2p", choices=["p2p", "nccl"])
     ap.add_argument("--sustain", type=float, default=1.0, help="seconds of back-to-back replay for clock sampling")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--refl-depth", type=int, default=1, choices=[1, 2],
+                    help="reflection bounces (2 = BASELINE config 5; beyond the reference, whose arm then runs its depth-2 patched copy)")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--ncu-child", action="store_true", help="internal: the frames ncu profiles for the roofline")
     return ap.parse_args()
@@ -95,6 +97,9 @@ def host_threads():
 _REF_CACHE = {}
 
 
+REFL_DEPTH = 1
+
+
 def reference_frames(w, W, H, frames, threads, first_step=0):
     """Times the reference's own Render() (SSE packet tracer, oracle/_ref) on the host cores. Returns
     (total_rays, total_seconds, variant, cpu_utilisation = process CPU time / wall time).
@@ -106,6 +111,8 @@ def reference_frames(w, W, H, frames, threads, first_step=0):
     import snailref as R
     import snail_b200 as sb
     variant = "sse" if R.available("sse") else "scalar"
+    if REFL_DEPTH == 2:  # oracle/_ref/libsnailref_depth2.so: the scalar build with `cache.reflections < 2` (oracle/build_ref.sh)
+        variant = "depth2"
     key = (w["name"], variant)
     if key not in _REF_CACHE:
         ref = R.RefScene(w["obj_path"], w["mtl_path"], w["tex_dir"], variant=variant)
@@ -196,6 +203,7 @@ def ncu_child(args, w, W, H):
     sc = sb.Scene(0)
     sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"])
     sc.set_options(w["gvals"])
+    sc.set_reflection_depth(args.refl_depth)
     bmin, bmax = sc.bbox()
     frame, _ = sc.frame_create(W, H)
     for i in range(3):
@@ -217,7 +225,7 @@ def ncu_pass(args, W, H, variant):
     env = dict(os.environ, SNL_RENDER_VARIANT=str(max(0, variant)), CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", "0"))
     cmd = [ncu, "--metrics", ",".join(NCU_METRICS), "--clock-control", "none", "-k", "regex:k_render", "--launch-skip", "2",
            "--launch-count", "1", "--csv", sys.executable, os.path.abspath(__file__), "--ncu-child", "--workload", args.workload,
-           "--res", args.res, "--warmup", str(args.warmup)]
+           "--res", args.res, "--warmup", str(args.warmup), "--refl-depth", str(args.refl_depth)]
     try:
         r = subprocess.run(cmd, capture_output=True, text=True, timeout=420, env=env)
     except Exception as e:  # noqa: BLE001
@@ -326,6 +334,7 @@ def run_ours(args, w, W, H):
     sc = sb.Scene(local_rank)
     sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"])
     sc.set_options(w["gvals"])
+    sc.set_reflection_depth(args.refl_depth)
     bmin, bmax = sc.bbox()
     stream = torch.cuda.ExternalStream(sc.stream(), device=dev)
     pitch = W * 3
@@ -525,6 +534,10 @@ def main():
     from snail_b200 import workloads
     w = workloads.resolve(args.workload)
     W, H = [int(x) for x in args.res.lower().split("x")]
+    global REFL_DEPTH
+    REFL_DEPTH = args.refl_depth
+    if args.refl_depth == 2:
+        w["desc"] += "; TWO reflection bounces (beyond the reference's cap of one)"
     if args.ncu_child:
         ncu_child(args, w, W, H)
     elif args.impl == "reference":

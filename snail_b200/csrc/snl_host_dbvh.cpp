@@ -1,5 +1,6 @@
-// snail_b200 — host side of the instanced two-level BVH: ObjectInstance::ComputeBBox and
-// DBVH::Construct / FindSplit (src/dbvh/tree.cpp:4-21,40-185) restated so that the top-level tree AND the order the
+// snail_b200 — host side of the instanced two-level BVH. A PORT, not new work:
+// ObjectInstance::ComputeBBox and DBVH::Construct / FindSplit (src/dbvh/tree.cpp:4-21,40-185) are restated function for
+// function (same bins, same locals, the same std::partition on the same range) so that the top-level tree AND the order the
 // builder leaves the instances in (std::partition) are the reference's: Context::object is an index into that order.
 // Compiled with -ffp-contract=off like the rest of the host code.
 #include <algorithm>
