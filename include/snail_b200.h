@@ -292,6 +292,10 @@ int snl_comm_create_root(snl_scene *, int world, int W, int H, unsigned char blo
 int snl_comm_attach(snl_scene *, int rank, const unsigned char blob[SNL_COMM_BLOB_BYTES], snl_comm **out);
 int snl_comm_create_local(snl_scene *const *scenes, int n, int W, int H, snl_comm **out);
 int snl_comm_info(const snl_comm *, int *world, int *W, int *H, int *localRanks);
+/* The work split of snl_render_multi without a device (host logic only): the packets {x, y, w, h} rank `rank` of `world`
+ * renders of a W x H frame, row bands in order; bandFirst[b] .. bandFirst[b + 1] (9 entries) = its packets of band b.
+ * packets_xywh may be NULL to ask for the count (at most ceil(W/16) * ceil(H/16) packets). */
+int snl_comm_plan(int world, int W, int H, int rank, int *packets_xywh, int *nPackets, int *nBands, int *bandFirst);
 int snl_render_multi(snl_comm *, const snl_camera *cam, unsigned char *bgr8_host, size_t pitch, snl_stats *stats);
 /* device pointer (rank 0's address space) + pitch of the frame the last snl_render_multi produced */
 int snl_comm_frame(snl_comm *, void **bgr8_dev, size_t *pitch);

@@ -25,7 +25,7 @@ ABI_SYMBOLS = [
     "snl_scene_set_host_scene", "snl_scene_build_device", "snl_scene_build_ms", "snl_scene_set_device_builder", "snl_host_build_binned_sah", "snl_scene_set_instances",
     "snl_trace_primary_inst", "snl_scene_copy_dbvh", "snl_host_dbvh_build", "snl_frame_create", "snl_frame_open", "snl_frame_close", "snl_frame_read",
     "snl_measure_peaks", "snl_comm_create_root", "snl_comm_attach", "snl_comm_create_local", "snl_comm_info", "snl_render_multi",
-    "snl_comm_frame", "snl_comm_destroy",
+    "snl_comm_frame", "snl_comm_destroy", "snl_comm_plan",
 ]
 
 # reference record layouts (src/bvh/tree.h:60-72, src/triangle.h:133-135,181-230)
@@ -173,6 +173,7 @@ def load_library(counters: bool = False) -> C.CDLL:
     L.snl_comm_info.argtypes = [vp, ip, ip, ip, ip]
     L.snl_render_multi.argtypes = [vp, C.POINTER(Camera), vp, C.c_size_t, C.POINTER(Stats)]
     L.snl_comm_frame.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_size_t)]
+    L.snl_comm_plan.argtypes = [i, i, i, i, vp, ip, ip, vp]
     L.snl_comm_destroy.argtypes = [vp]
     L.snl_comm_destroy.restype = None
     _libs[path] = L
@@ -525,6 +526,19 @@ class Scene:
 
 
 COMM_BLOB_BYTES = 96
+
+
+def comm_plan(world: int, W: int, H: int, rank: int):
+    """snl_comm_plan: (packets (n, 4) int32 {x, y, w, h} of `rank` in launch order, number of row bands, bandFirst[9])."""
+    L = load_library()
+    n, nb = C.c_int(), C.c_int()
+    first = np.zeros(9, np.int32)
+    r = L.snl_comm_plan(world, W, H, rank, None, C.byref(n), C.byref(nb), _ptr(first))
+    if r:
+        raise SnlError(r, L.snl_last_error().decode())
+    packets = np.zeros((max(n.value, 1), 4), np.int32)
+    L.snl_comm_plan(world, W, H, rank, _ptr(packets), C.byref(n), C.byref(nb), _ptr(first))
+    return packets[: n.value], nb.value, first
 
 
 class Comm:

@@ -170,21 +170,27 @@ std::vector<int> deal_tiles(int nTiles, int world) {
 
 enum { kTilePackets = 4 };  // a tile = 4 packets of one packet row (64 x 16 pixels)
 
-int build_packet_list(snl_comm *c, CommRank &r) {
+// The packets {x, y, w, h} of `rank`, row bands in order, and where each band starts in the list (host only).
+void plan_packets(const snl_comm *c, int rank, std::vector<int4> &list, int bandFirst[kCommBands + 1]) {
 	const int W = c->W, H = c->H, px = (W + 15) / 16, py = (H + 15) / 16;
 	const int tilesX = (px + kTilePackets - 1) / kTilePackets;
 	const std::vector<int> owner = deal_tiles(tilesX * py, c->world);
-	std::vector<int4> list;
+	list.clear();
 	for(int b = 0; b < c->nBands; b++) {
-		r.bandFirst[b] = (int)list.size();
+		bandFirst[b] = (int)list.size();
 		for(int row = b * c->rowsPerBand; row < std::min(py, (b + 1) * c->rowsPerBand); row++)
 			for(int t = 0; t < tilesX; t++)
-				if(owner[row * tilesX + t] == r.rank)
+				if(owner[row * tilesX + t] == rank)
 					for(int col = t * kTilePackets; col < std::min(px, (t + 1) * kTilePackets); col++)
 						list.push_back(make_int4(col * 16, row * 16, std::min(16, W - col * 16), std::min(16, H - row * 16)));
 	}
 	for(int b = c->nBands; b <= kCommBands; b++)
-		r.bandFirst[b] = (int)list.size();
+		bandFirst[b] = (int)list.size();
+}
+
+int build_packet_list(snl_comm *c, CommRank &r) {
+	std::vector<int4> list;
+	plan_packets(c, r.rank, list, r.bandFirst);
 	SNL_CUDA(cudaSetDevice(r.scene->device));
 	const size_t n = std::max<size_t>(list.size(), 1);
 	for(int k = 0; k < 2; k++)
@@ -373,6 +379,23 @@ void snl_comm_destroy(snl_comm *c) {
 			cudaFree(c->ranks[0].seg);
 	}
 	delete c;
+}
+
+int snl_comm_plan(int world, int W, int H, int rank, int *packets_xywh, int *nPackets, int *nBands, int *bandFirst) {
+	SNL_REQUIRE(nPackets && rank >= 0 && rank < world, SNL_ERR_INVALID, "bad argument");
+	snl_comm c;
+	SNL_TRY(comm_geometry(&c, world, W, H));
+	std::vector<int4> list;
+	int first[kCommBands + 1];
+	plan_packets(&c, rank, list, first);
+	*nPackets = (int)list.size();
+	if(nBands)
+		*nBands = c.nBands;
+	if(bandFirst)
+		memcpy(bandFirst, first, sizeof(first));
+	if(packets_xywh)
+		memcpy(packets_xywh, list.data(), list.size() * sizeof(int4));
+	return SNL_OK;
 }
 
 int snl_comm_info(const snl_comm *c, int *world, int *W, int *H, int *localRanks) {

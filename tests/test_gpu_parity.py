@@ -365,3 +365,27 @@ def test_banded_host_render_equals_single_launch(sb):
     assert all((out["0"][0] == out[b][0]).all() and out["0"][1] == out[b][1] for b in ("4", "8"))
     assert out["4"][0].any()
     sc.close()
+
+
+def test_malformed_trees_are_refused_quickly(sb):
+    """snl_scene_set_geometry validates caller-supplied BVH::Node arrays: a child link that points back up the tree
+    (a cycle) or at a node another parent already owns must fail with a status, not recurse without end."""
+    import time
+    ref, sc = load_pair(sb, "box")
+    nodes, tris = ref.nodes().copy(), ref.tris()
+    good = sb.Scene(0)
+    good.set_geometry(nodes, tris)
+    good.close()
+    inner = np.nonzero(nodes["sub"] >= 0)[0]
+    bad = nodes.copy()
+    bad["sub"][inner[-1]] = 0  # the deepest inner node points back at the root: a cycle
+    shared = nodes.copy()
+    if len(inner) >= 2:
+        shared["sub"][inner[-1]] = shared["sub"][inner[0]]  # two parents own the same pair of children
+    for arr in (bad, shared):
+        t0 = time.time()
+        with pytest.raises(sb.SnlError) as e:
+            sc.set_geometry(arr, tris)
+        assert time.time() - t0 < 2.0 and "malformed" in str(e.value)
+    sc.close()
+    ref.close()
