@@ -386,6 +386,14 @@ def run_ours(args, w, W, H):
         # packets go into its frame). The library times every rank on the device with CUDA events on its stream, from the
         # moment the frame slot is open to the rank's last kernel (per-origin records, its packets, its publish): a rank
         # that is early for the slot does not count the wait. The K steps as a whole are bracketed by barrier + synchronize.
+        if fm.comm is None:  # "nccl" compose: static split + torch.distributed gather, timed around the whole call
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            with torch.cuda.stream(stream):
+                _, st = fm.render(cam, host=False)
+            e1.record(stream)
+            torch.cuda.synchronize(dev)
+            return e0.elapsed_time(e1), st["rays"]
         _, st = fm.render(cam, host=False)
         return st["kernel_ms"], st["rays"]
 
