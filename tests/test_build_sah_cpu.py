@@ -154,3 +154,30 @@ def test_degenerate_inputs(sb):
     nodes, order, height = sb.host_build_binned_sah(many)
     counts = [((~link) >> 26) + 1 for _, _, _, _, link, _ in walk(nodes) if link < 0]
     assert sum(counts) == 100 and max(counts) <= 32 and sorted(order.tolist()) == list(range(100))
+
+
+def test_bench_scene_quality(sb):
+    """The bench scene (268 K triangles): the binned-SAH tree's leaf cost against the reference's full-sweep tree, and
+    the build's level count (= stream synchronisations of the device build)."""
+    import time
+    from snail_b200 import workloads
+    try:
+        w = workloads.resolve("sponza_like_whitted")
+    except FileNotFoundError as e:
+        pytest.skip(str(e))
+    hs = sb.HostScene(w["obj_path"], w["mtl_path"], w["tex_dir"])
+    ref_nodes, tris, _, _ = hs.bvh()
+    t0 = time.time()
+    nodes, order, height = sb.host_build_binned_sah(tris)
+    dt = time.time() - t0
+    leaf_cost = 0.0
+    for _, _, lo, hi, link, _ in walk(nodes):
+        if link < 0:
+            leaf_cost += float(sa(lo, hi)) * (((~link) >> 26) + 1)
+    rl = ref_nodes[(ref_nodes["sub"] & -0x80000000) != 0]
+    ref_counts = (rl["axis"].astype(np.int64) & 0xffff) | (rl["first_node"].astype(np.int64) << 16)
+    ref_cost = float((sa(rl["bmin"].astype(np.float64), rl["bmax"].astype(np.float64)) * ref_counts).sum())
+    print(f"sponza_like: {len(tris)} triangles -> {len(nodes)} inner nodes, height {height} (reference tree depth {hs.depth}), host run "
+          f"{dt:.2f} s; leaf SA cost {leaf_cost / ref_cost:.3f}x the reference's full-sweep tree")
+    assert sorted(order.tolist()) == list(range(len(tris)))
+    assert leaf_cost <= 1.05 * ref_cost and height <= 40
