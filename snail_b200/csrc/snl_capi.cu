@@ -1152,9 +1152,11 @@ static int render_common(snl_scene *s, const snl_camera *cam, int W, int H, cons
 	const int variant = T.choice;
 	const char *bandsEnv = getenv("SNL_RENDER_BANDS");  // number of bands; "0" / "1": one launch, copy afterwards
 	// frames of a millisecond and more hide more of the copy with eight bands (+1.2 % e2e on sponza_like); short ones lose
-	// more to the extra launches than they gain (-1 % on feline): four
+	// more to the extra launches than they gain (-1 % on feline): four - unless the frame itself is big: a 24.9 MB 4K frame
+	// takes 0.45 ms to copy, and eight bands expose half as much of it as four (0.814 vs 0.858 ms on barracks 4K)
+	const bool bigFrame = (size_t)W * H * 3 >= ((size_t)12 << 20);
 	const int nBands = bandsEnv ? std::min(atoi(bandsEnv), (int)snl_scene::kMaxBands)
-								: (s->lastCallMs > 0.8f ? (int)snl_scene::kMaxBands : (int)snl_scene::kBands);
+								: (s->lastCallMs > 0.8f || bigFrame ? (int)snl_scene::kMaxBands : (int)snl_scene::kBands);
 	if(hostOut && hostDone && !packets && nPk >= 8 * s->smCount && nBands > 1) {
 		SNL_TRY(ensure_band_streams(s));
 		const int px = (W + 15) / 16, py = (H + 15) / 16;
