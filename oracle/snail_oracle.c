@@ -67,6 +67,8 @@ typedef struct oracle_scene {
 	int nLights;
 	float ambient[3];
 	int gVals[16];
+	int maxRefl; /* bounces followed: 1 = the reference (`cache.reflections < 1`, src/scene_trace.cpp:454); 2 = that condition
+	              * relaxed to `< 2`, the comparison for BASELINE config 5 (oracle/_ref/libsnailref_depth2.so) */
 	/* instrumentation of the last call */
 	unsigned char *undefLanes; /* when set: packet_raytrace reports the lanes the reference shades from uninitialised memory */
 	uint64_t nodeVisits, triTests, rays[5]; /* primary, shadow, reflection, reflection shadow, transparency */
@@ -503,7 +505,7 @@ static void packet_raytrace_ex(oracle_scene *s, const OPacket *pk, int level, in
 	for(int b0 = 0; b0 < pk->n; b0 += 16)
 		shade_block(s, pk, b0, hit, sel, packetHasMask, sm, trans, undef);
 
-	if(level == 0 && s->gVals[7]) { /* TraceReflection :603-618, blend :454-466 */
+	if(level < s->maxRefl && s->gVals[7]) { /* TraceReflection :603-618, blend :454-466 */
 		OPacket rp;
 		float rc[256][3];
 		rp.n = pk->n;
@@ -518,7 +520,7 @@ static void packet_raytrace_ex(oracle_scene *s, const OPacket *pk, int level, in
 			rp.active[i] = sel[i];
 		}
 		unsigned char ru[256] = {0};
-		packet_raytrace_ex(s, &rp, 1, 0, 0, !all, rc, ru);
+		packet_raytrace_ex(s, &rp, level + 1, 0, 0, !all, rc, ru);
 		for(int i = 0; i < pk->n; i++)
 			undef[i] |= sel[i] && ru[i];
 		for(int i = 0; i < pk->n; i++)
@@ -611,6 +613,7 @@ static void packet_raytrace(oracle_scene *s, const OPacket *pk, int level, int s
 oracle_scene *oracle_create(const void *nodes, int nNodes, const void *tris, const void *shtris, int nTris,
 							const int32_t *matIds, int nMatIds, const void *mats, int nMats, const void *texs, int nTex) {
 	oracle_scene *s = (oracle_scene *)calloc(1, sizeof(oracle_scene));
+	s->maxRefl = 1;
 	s->nodes = (const ONode *)nodes;
 	s->tris = (const OTri *)tris;
 	s->shtris = (const OShTri *)shtris;
@@ -627,6 +630,7 @@ oracle_scene *oracle_create(const void *nodes, int nNodes, const void *tris, con
 }
 void oracle_destroy(oracle_scene *s) { free(s); }
 void oracle_set_gvals(oracle_scene *s, const int *g) { memcpy(s->gVals, g, sizeof(s->gVals)); }
+void oracle_set_reflection_depth(oracle_scene *s, int depth) { s->maxRefl = depth < 1 ? 1 : depth > 2 ? 2 : depth; }
 void oracle_set_lights(oracle_scene *s, const float *l7, int n) { /* pos, color, radius */
 	s->nLights = n;
 	for(int i = 0; i < n; i++) {

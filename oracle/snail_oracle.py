@@ -32,6 +32,7 @@ def lib():
         _lib.oracle_create.argtypes = [vp, i, vp, vp, i, vp, i, vp, i, vp, i]
         _lib.oracle_destroy.argtypes = [vp]
         _lib.oracle_set_gvals.argtypes = [vp, vp]
+        _lib.oracle_set_reflection_depth.argtypes = [vp, i]
         _lib.oracle_set_lights.argtypes = [vp, vp, i]
         _lib.oracle_counts.argtypes = [vp, vp]
         _lib.oracle_trace_primary.argtypes = [vp, vp, i, i, vp, vp, vp]
@@ -93,6 +94,10 @@ class OracleScene:
         for k, v in (gvals.items() if isinstance(gvals, dict) else enumerate(gvals)):
             g[k] = v
         self.L.oracle_set_gvals(self.h, _p(g))
+
+    def set_reflection_depth(self, depth):
+        """1 = the reference's cap; 2 = `cache.reflections < 2` (oracle/_ref/libsnailref_depth2.so is the reference patched so)."""
+        self.L.oracle_set_reflection_depth(self.h, int(depth))
 
     def set_lights(self, lights):
         a = np.ascontiguousarray(np.array(lights, np.float32).reshape(-1, 7))

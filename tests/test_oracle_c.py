@@ -7,7 +7,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import DATA, GOLDEN, ROOT
+from conftest import DATA, GOLDEN, ROOT, need_oracle, scene_path
 
 MANIFEST = json.load(open(os.path.join(GOLDEN, "manifest.json")))
 STAGES = {"simple_nolight": ({}, False), "depth": ({1: 1}, False), "simple_light": ({}, True),
@@ -78,3 +78,38 @@ def test_c_oracle_frames_vs_golden(sb, name):
         assert frac >= 0.999, (stage, frac)
         assert abs(st["rays"] - c["rays"][stage]) <= max(4 * int(undef.sum()), 0.002 * c["rays"][stage]), stage
     orc.close()
+
+
+@pytest.mark.parametrize("name,inside,W,H", [("box", True, 160, 96), ("lancia", False, 192, 128), ("feline", False, 160, 96)])
+def test_two_bounces_restatement_vs_patched_reference(name, inside, W, H):
+    """Reflection depth 2 (BASELINE config 5) is beyond the reference's cap; its comparison is the reference with
+    `cache.reflections < 1` relaxed to `< 2` (oracle/_ref/libsnailref_depth2.so, oracle/build_ref.sh). The plain-C
+    restatement with the same relaxation must reproduce that library's frames and ray counts, which pins the depth-2
+    semantics (second bounce shaded and lit like the first, 0.3 blend at both levels) twice."""
+    R = need_oracle("depth2")
+    import snail_oracle as O
+    ref = R.RefScene(scene_path(name), variant="depth2")
+    orc = O.OracleScene(ref.nodes(), ref.tris(), ref.shtris() if ref.n_shtris else None, ref.matids())
+    cam, light = R.bench_camera(*ref.bbox(), inside=inside)
+    gv = {6: 1, 7: 1}
+    ref.set_gvals(gv)
+    ref.set_lights([light])
+    img_r, st_r, _ = ref.render(cam, W, H, threads=1)
+    orc.set_gvals(gv)
+    orc.set_lights([light])
+    orc.set_reflection_depth(1)
+    img_1, c1 = orc.render(cam, W, H)
+    orc.set_reflection_depth(2)
+    undef = np.zeros((H, W), np.uint8)
+    img_2, c2 = orc.render(cam, W, H, undef=undef)
+    err = np.abs(img_2.astype(np.int16) - img_r.astype(np.int16)).max(axis=2)
+    err[undef != 0] = 0
+    print(f"{name}: two bounces, restatement vs patched reference: within 1/255 on {(err <= 1).mean()*100:.3f} %; rays {c2['rays']} vs "
+          f"{st_r['rays']} (one bounce {c1['rays']})")
+    assert (err <= 1).mean() >= 0.999
+    # (the per-ray restatement casts a few shadow rays less than the packet code where a packet straddles the light's reach -
+    # at either depth: 0.12 % on this lancia frame with ONE bounce too)
+    assert abs(c2["rays"] - st_r["rays"]) <= max(4 * int((undef != 0).sum()), 0.005 * st_r["rays"])
+    assert c2["reflection"] > c1["reflection"] and c2["primary"] == c1["primary"]
+    orc.close()
+    ref.close()
