@@ -42,6 +42,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--refl-depth", type=int, default=1, choices=[1, 2],
                     help="reflection bounces (2 = BASELINE config 5; beyond the reference, whose arm then runs its depth-2 patched copy)")
+    ap.add_argument("--tree", default="host", choices=["host", "lbvh", "sah"],
+                    help="which tree the GPU arm walks: host = the reference's SAH sweep tree (bit-identical port, default), "
+                         "lbvh / sah = built on the device (Morton LBVH / binned SAH, snl_build*.cu)")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--ncu-child", action="store_true", help="internal: the frames ncu profiles for the roofline")
     return ap.parse_args()
@@ -332,7 +335,8 @@ def run_ours(args, w, W, H):
         dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
 
     sc = sb.Scene(local_rank)
-    sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"])
+    build_flags = {"host": sb.USE_SAH, "lbvh": sb.BUILD_DEVICE, "sah": sb.BUILD_DEVICE | sb.BUILD_SAH_BINNED}[args.tree]
+    sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"], build_flags=build_flags)
     sc.set_options(w["gvals"])
     sc.set_reflection_depth(args.refl_depth)
     bmin, bmax = sc.bbox()
@@ -546,6 +550,8 @@ def main():
     REFL_DEPTH = args.refl_depth
     if args.refl_depth == 2:
         w["desc"] += "; TWO reflection bounces (beyond the reference's cap of one)"
+    if args.tree != "host":
+        w["desc"] += f"; tree built on the device ({'Morton LBVH' if args.tree == 'lbvh' else 'binned SAH'}) instead of the reference's"
     if args.ncu_child:
         ncu_child(args, w, W, H)
     elif args.impl == "reference":
