@@ -59,3 +59,20 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 src = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "snailref" not in src and "oracle/" not in src.replace("never touches oracle/", ""), f
+
+
+def test_header_is_plain_c_and_the_c_caller_links(sb, tmp_path):
+    """include/snail_b200.h must be usable from C (no C++-isms, no torch / CUDA types), and the plain-C multi-GPU caller
+    of tests/c links against the library and refuses to run - cleanly, with a message - on a box without a device."""
+    import subprocess
+    inc, lib_dir = os.path.join(ROOT, "include"), os.path.join(ROOT, "snail_b200")
+    probe = tmp_path / "probe.c"
+    probe.write_text('#include "snail_b200.h"\nint main(void) { return sizeof(snl_camera) + sizeof(snl_stats) > 0 ? 0 : 1; }\n')
+    subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Wextra", "-Werror", "-fsyntax-only", "-I", inc, str(probe)], check=True)
+    exe = str(tmp_path / "render_multi_test")
+    subprocess.run(["gcc", "-std=c11", "-O1", "-Wall", "-Werror", "-I", inc, os.path.join(ROOT, "tests", "c", "render_multi_test.c"),
+                    "-L", lib_dir, "-lsnail_b200", "-lm", f"-Wl,-rpath,{lib_dir}", "-o", exe], check=True)
+    if sb.load_library().snl_device_count() > 0:
+        return  # the GPU suite runs it for real (tests/test_gpu_multi.py)
+    r = subprocess.run([exe, os.path.join(ROOT, "data", "box.obj"), "1", "64", "64", "1"], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 2 and "0 visible" in r.stderr, (r.returncode, r.stdout, r.stderr)
