@@ -18,6 +18,15 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 
 
+def pytest_collection_modifyitems(config, items):
+    """A stuck test (a lost collective, a wedged device) must fail, not hold the box: 20 minutes per test where
+    pytest-timeout is installed (the slowest test takes about one)."""
+    if config.pluginmanager.hasplugin("timeout"):
+        for item in items:
+            if item.get_closest_marker("timeout") is None:
+                item.add_marker(pytest.mark.timeout(1200))
+
+
 COMPARE_IMG = os.path.join(ROOT, "tools", "compare_img")
 
 
