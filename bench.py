@@ -185,13 +185,14 @@ def walker_counts(name, W, H):
         return None
 
 
-def counters_build_counts(sb, w, W, H, cam, light):
+def counters_build_counts(sb, w, W, H, cam, light, args=None):
     """Fallback for workloads without committed walker counts: the same kernels built with -DSNL_COUNTERS."""
     if not os.path.exists(sb.api.LIB_COUNTERS_PATH):
         return None
     sc = sb.Scene(0, counters=True)
-    sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"])
+    sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"], build_flags=tree_flags(sb, args.tree if args else "host"))
     sc.set_options(w["gvals"])
+    sc.set_reflection_depth(args.refl_depth if args else 1)
     sc.set_lights([light] if w["lit"] else [])
     _, st = sc.render(cam, W, H)
     sc.close()
@@ -199,12 +200,17 @@ def counters_build_counts(sb, w, W, H, cam, light):
             "shaded_hits": st["reflection"] + st["reflection"], "source": "snail_b200 kernels built with -DSNL_COUNTERS"}
 
 
+def tree_flags(sb, tree):
+    """--tree: the reference's SAH sweep tree from the host port (default) or one of the two device builders."""
+    return {"host": sb.USE_SAH, "lbvh": sb.BUILD_DEVICE, "sah": sb.BUILD_DEVICE | sb.BUILD_SAH_BINNED}[tree]
+
+
 def ncu_child(args, w, W, H):
     """`bench.py --ncu-child` (run under ncu by ncu_pass): three device-resident frames of the workload at the bench
     camera with the kept register-budget variant pinned; ncu profiles the third k_render launch."""
     import snail_b200 as sb
     sc = sb.Scene(0)
-    sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"])
+    sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"], build_flags=tree_flags(sb, args.tree))
     sc.set_options(w["gvals"])
     sc.set_reflection_depth(args.refl_depth)
     bmin, bmax = sc.bbox()
@@ -228,7 +234,7 @@ def ncu_pass(args, W, H, variant):
     env = dict(os.environ, SNL_RENDER_VARIANT=str(max(0, variant)), CUDA_VISIBLE_DEVICES=os.environ.get("CUDA_VISIBLE_DEVICES", "0"))
     cmd = [ncu, "--metrics", ",".join(NCU_METRICS), "--clock-control", "none", "-k", "regex:k_render", "--launch-skip", "2",
            "--launch-count", "1", "--csv", sys.executable, os.path.abspath(__file__), "--ncu-child", "--workload", args.workload,
-           "--res", args.res, "--warmup", str(args.warmup), "--refl-depth", str(args.refl_depth)]
+           "--res", args.res, "--warmup", str(args.warmup), "--refl-depth", str(args.refl_depth), "--tree", args.tree]
     try:
         r = subprocess.run(cmd, capture_output=True, text=True, timeout=420, env=env)
     except Exception as e:  # noqa: BLE001
@@ -265,7 +271,8 @@ def build_roofline(sb, args, w, W, H, sc, ms_per_launch, clocks, rank):
         pass
     hbm_peak = float(driver.get("hbm_gbs", 6650.0))
     n, err = ncu_pass(args, W, H, sc.render_variant())
-    wc = walker_counts(w["name"], W, H) or counters_build_counts(sb, w, W, H, cam, light)
+    wc = walker_counts(w["name"], W, H) if args.tree == "host" and args.refl_depth == 1 else None  # committed counts: the reference's tree, one bounce
+    wc = wc or counters_build_counts(sb, w, W, H, cam, light, args)
     rf = {"bound": "issue", "unit": "Gwarp-inst/s", "kernel": "k_render",
           "peak": round(peaks["issue_peak_gwarpinst_s"], 1),
           "peak_source": f"{peaks['sms']} SMs x 4 schedulers x {peaks['sm_clock_mhz_max']:.0f} MHz; an FFMA / integer-ALU interleave "
@@ -335,8 +342,7 @@ def run_ours(args, w, W, H):
         dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
 
     sc = sb.Scene(local_rank)
-    build_flags = {"host": sb.USE_SAH, "lbvh": sb.BUILD_DEVICE, "sah": sb.BUILD_DEVICE | sb.BUILD_SAH_BINNED}[args.tree]
-    sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"], build_flags=build_flags)
+    sc.load_obj(w["obj_path"], w["mtl_path"], w["tex_dir"], build_flags=tree_flags(sb, args.tree))
     sc.set_options(w["gvals"])
     sc.set_reflection_depth(args.refl_depth)
     bmin, bmax = sc.bbox()
