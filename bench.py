@@ -348,7 +348,7 @@ def run_ours(args, w, W, H):
     bmin, bmax = sc.bbox()
     stream = torch.cuda.ExternalStream(sc.stream(), device=dev)
     pitch = W * 3
-    # N > 1: farm.Farm = bootstrap of snl_comm_* / snl_render_multi ("p2p": shared cursor, peer stores into rank 0's
+    # N > 1: farm.Farm = bootstrap of snl_comm_* / snl_render_multi ("p2p": static deal, peer stores into rank 0's
     # frame, in-stream completion, banded device->host copy) or the static tile split + NCCL gather ("nccl")
     fm = farm.Farm(sc, dist, W, H, compose="p2p" if args.compose == "p2p" else "gather") if world > 1 else None
     frame = sc.frame_create(W, H)[0] if world == 1 else None
@@ -492,8 +492,9 @@ def run_ours(args, w, W, H):
             dist.destroy_process_group()
         return
     value = total_rays / (total_ms * 1e-3) / 1e6
-    compose = {1: "none (1 GPU)"}.get(world, "p2p (snl_render_multi): every rank's persistent k_render fetches packet batches from a shared cursor "
-                                             "and stores them into rank 0's frame through CUDA-IPC peer memory (NVLink), in-stream completion"
+    compose = {1: "none (1 GPU)"}.get(world, "p2p (snl_render_multi): packets dealt to the ranks like the reference's taskMap; every rank's k_render stores its share "
+                                             "into rank 0's frame through CUDA-IPC peer memory (NVLink), one launch + one system-scope signal per row band, "
+                                             "in-stream completion"
                                       if args.compose == "p2p" else "static 16x64 tile split + NCCL gather of packed tiles to rank 0")
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": K,

@@ -275,11 +275,14 @@ int snl_frame_read(snl_scene *, const void *bgr8_dev, int W, int H, unsigned cha
 /* Render() over the GPUs of one box behind this ABI: replaces the reference's farm loop (src/server.cpp:227-265 tile
  * split, :330-418 receive loop + stats merge; src/node.cpp:308-346 node side; src/comm_mpi.cpp transport). Every GPU
  * holds a replica of the scene (one snl_scene each, same geometry / materials / lights / options); the frame lives in
- * rank 0's HBM in a segment the other ranks map. Per frame all ranks run ONE persistent k_render each that fetches
- * packet batches from a shared cursor (system-scope atomics over NVLink: the GPUs balance themselves, where the
- * reference dealt tiles statically), stores its packets straight into rank 0's frame and counts them off per row band;
- * rank 0 copies band i to the host while band i+1 is still rendering, and sums the TreeStats. No host-side collective
- * per frame; every device-side wait has a time-out (SNL_ERR_STATE) instead of a hang.
+ * rank 0's HBM in a segment the other ranks map. The frame's packets are dealt to the ranks like the reference's taskMap
+ * (tiles of 4 packets, every run of `world` tiles in a freshly shuffled order; snl_comm_plan returns the split). Per
+ * frame every rank runs one k_render per row band of its share, storing its packets straight into rank 0's frame over
+ * NVLink, and signals the band with ONE system-scope increment behind the kernel boundary; rank 0 copies band i to the
+ * host while band i+1 is still rendering on all GPUs, and sums the TreeStats. From the second frame on a band's packets
+ * run longest first (cycles measured in the previous frame). No host-side collective per frame; every device-side wait
+ * has an 8 s time-out that comes back as SNL_ERR_STATE instead of a hang (the communicator is then dead: destroy it).
+ * A cursor-fed persistent k_render was built and measured slower.
  *   between processes (one rank per process, e.g. under torchrun / mpirun):
  *       rank 0:  snl_comm_create_root(scene, world, W, H, blob, &comm);  send blob to the others with ANY byte transport
  *       rank r:  snl_comm_attach(scene, r, blob, &comm);

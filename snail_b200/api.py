@@ -543,7 +543,8 @@ def comm_plan(world: int, W: int, H: int, rank: int):
 
 class Comm:
     """Render() over the GPUs of one box (snl_comm_* / snl_render_multi, include/snail_b200.h): the frame lives on rank
-    0, every rank's persistent k_render pulls packet batches from a shared cursor and stores into it over NVLink.
+    0, the packets are dealt to the ranks like the reference's taskMap and every rank's k_render stores its share into it
+    over NVLink, one launch + one completion signal per row band.
 
       Comm.root(scene, world, W, H) -> (comm, blob)    rank 0; send `blob` (96 bytes) to the others by any transport
       Comm.attach(scene, rank, blob)                   ranks 1..world-1 (other processes)

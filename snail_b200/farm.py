@@ -5,9 +5,9 @@ are partitioned, secondary rays never leave the GPU that spawned them.
 
 Two compose paths:
   * "p2p"  — snl_comm_* / snl_render_multi (snail_b200/csrc/snl_comm.cu, C++ behind the C ABI): rank 0 owns the
-             frame, every other rank maps it through CUDA IPC and its persistent k_render stores packets straight
-             into rank 0's HBM over NVLink/NVSwitch, fetching them from a shared cursor: compute and gather are ONE
-             kernel, no staging buffer, no collective on the data path. This module only bootstraps it.
+             frame, every other rank maps it through CUDA IPC and its k_render stores its share of the packets (a static
+             deal like the reference's taskMap) straight into rank 0's HBM over NVLink/NVSwitch: compute and gather
+             are ONE kernel, no staging buffer, no collective on the data path. This module only bootstraps it.
   * "gather" — every rank packs its tiles into a contiguous buffer, torch.distributed gathers the buffers on
              rank 0 (NCCL on GPUs, gloo in the CPU tests), rank 0 scatters them into the frame.
 """
@@ -122,8 +122,8 @@ class Farm:
     """Render() over the ranks of one box: the counterpart of the reference's server loop (src/server.cpp:266-420)
     with `dist` = an initialised torch.distributed process group (used ONLY to hand rank 0's 96-byte bootstrap blob to
     the other ranks, and by the "gather" compose) and `scene` = this rank's snail_b200.Scene holding a replica of the
-    scene. compose = "p2p" (default): a thin caller of snl_comm_* / snl_render_multi (C++ behind the ABI: shared
-    cursor, peer stores into rank 0's frame, in-stream completion, banded device->host copy; no per-frame host
+    scene. compose = "p2p" (default): a thin caller of snl_comm_* / snl_render_multi (C++ behind the ABI: static
+    deal, peer stores into rank 0's frame, in-stream completion, banded device->host copy; no per-frame host
     collective, two frame slots so a rank can start frame k+1 while rank 0 still reads frame k). compose = "gather":
     static tile split + torch.distributed gather of packed tiles (the NCCL collective north_star words; kept as the
     cross-check and for boxes without peer access)."""

@@ -1,5 +1,5 @@
 """Multi-GPU Render() behind the C ABI (snl_comm_* / snl_render_multi) and its Python bootstrap (farm.Farm).
-  * world = 1 (runs on any GPU box): the persistent, cursor-fed k_render with band counters and the banded
+  * world = 1 (runs on any GPU box): the per-band k_render launches with band signals and the banded
     device->host copy against the plain snl_render: frames byte-identical, TreeStats equal, on every kernel flavour
     (plain, transparency, instanced) and on frame sizes that are not multiples of the packet / the 16-byte store;
   * the plain-C caller tests/c/render_multi_test.c (no Python, no torch) on min(2, GPUs) devices in ONE process;

@@ -1,6 +1,7 @@
 #!/usr/bin/env python
-"""GPU box, 1 GPU: the persistent cursor-fed k_render of snl_render_multi (world = 1) against the static launch of
-snl_render_dev on the same frames - what the dynamic fetch, the per-batch release and the banded copy cost by themselves.
+"""GPU box, 1 GPU: snl_render_multi (world = 1: frame protocol, per-band launches + signals, banded copy) against the
+single launch of snl_render_dev on the same frames - what the multi-GPU machinery costs by itself. (Written for the
+cursor-fed persistent k_render of profiles/r2f / r2g, which lost and was removed.)
     python tools/bench_comm.py [workload res]..."""
 import os
 import sys
