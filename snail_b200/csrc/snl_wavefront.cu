@@ -120,8 +120,8 @@ __global__ void __launch_bounds__(kPacket) k_wf_primary(SceneDev S, const PreSet
 // Every lane owns one ray at a time. At the top of the loop the warp hands new rays to the lanes that finished theirs:
 // rays come from a warp-private chunk [wnext, wend) of the queue, refilled with one atomicAdd on the global cursor per
 // kChunk rays. Then all lanes with a ray run one round of the while-while walk (inner nodes until every lane has parked
-// a leaf or run dry, then the parked leaves). SHADOW = any-hit from a light origin (translated nodes + PreTri of that
-// light), else nearest hit with a per-ray origin (plain nodes + GenTri).
+// a leaf or run dry, then the parked leaves). SHADOW = any-hit from a light origin (the one node array + PreTri of that
+// light), else nearest hit with a per-ray origin (same nodes + GenTri).
 enum { kChunk = 64 };
 
 #ifndef SNL_WF_MIN_BLOCKS
